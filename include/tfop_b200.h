@@ -1,0 +1,121 @@
+/* libtfop_b200 — C ABI of the B200 (sm_100a) replica-runtime kernels.
+ *
+ * Every function returns 0 on success; on failure it returns non-zero and
+ * tfop_last_error() gives a thread-local description. Streams are passed as
+ * cudaStream_t (a CUstream handle; torch.cuda.current_stream().cuda_stream
+ * works). dtype tags: 0 = fp32, 1 = bf16.
+ *
+ * The reference (ryantd/tf-operator) ships no native code at all (SURVEY.md
+ * 2.8c); each entry point below cites the reference call site whose path it
+ * replaces.
+ */
+#ifndef TFOP_B200_H_
+#define TFOP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+typedef struct tfop_comm tfop_comm;
+
+enum { TFOP_DT_F32 = 0, TFOP_DT_BF16 = 1 };
+
+const char* tfop_last_error(void);
+int tfop_version(void);
+
+/* ---- symmetric peer memory (csrc/symm.cu) -------------------------------
+ * Replaces the DNS-name + port addressing of pkg/controller.v1/pytorch/
+ * pytorch.go:13-68 with CUDA IPC handles exchanged at rendezvous. */
+int tfop_comm_handle_bytes(void);
+int tfop_comm_create(int rank, int world, size_t data_bytes, tfop_comm** out);
+int tfop_comm_get_handle(tfop_comm* c, void* out_bytes);
+int tfop_comm_open_peers(tfop_comm* c, const void* all_handles);
+int tfop_comm_create_emulated(int world, size_t data_bytes, tfop_comm** out);
+void* tfop_comm_buffer(tfop_comm* c, int peer);
+size_t tfop_comm_buffer_bytes(tfop_comm* c);
+int tfop_comm_rank(tfop_comm* c);
+int tfop_comm_world(tfop_comm* c);
+int tfop_comm_check_error(tfop_comm* c, int* flag);
+int tfop_comm_destroy(tfop_comm* c);
+
+/* ---- K1/K6/K8: fused P2P all-reduce (csrc/allreduce.cu) ------------------
+ * Replaces the NCCL all-reduce of examples/v1/distribution_strategy/keras-API/
+ * multi_worker_strategy-with-keras.py:76-77 and the rabit histogram
+ * all-reduce of examples/xgboost/xgboostjob.yaml:19-25. algo: 0 auto,
+ * 1 one-shot, 2 two-shot. */
+int tfop_allreduce(tfop_comm* c, const void* in, int in_dtype, void* out, int out_dtype,
+                   int wire_dtype, size_t n, size_t sym_off, float scale, int algo,
+                   int max_blocks, cudaStream_t stream);
+int tfop_allreduce_emulated(tfop_comm** comms, int world, const void* const* ins, int in_dtype,
+                            void* const* outs, int out_dtype, int wire_dtype, size_t n,
+                            size_t sym_off, float scale, int algo, int max_blocks,
+                            cudaStream_t stream);
+int tfop_allreduce_set_oneshot_max_bytes(size_t bytes);
+
+/* ---- fused flat-buffer optimizers (csrc/optim.cu) ------------------------
+ * The optimizer step that follows the gradient exchange in
+ * examples/v1/dist-mnist/dist_mnist.py:194-208. hp_dev: device float[8] =
+ * {lr, momentum, weight_decay, grad_scale, beta1, beta2, eps, step}. */
+int tfop_sgd_momentum(float* master, float* mom, const void* grad, int grad_dtype,
+                      void* weights_bf16, size_t n, size_t n_decay, const float* hp_dev,
+                      int nesterov, cudaStream_t stream);
+int tfop_adamw(float* master, float* m1, float* m2, const void* grad, int grad_dtype,
+               void* weights_bf16, size_t n, size_t n_decay, const float* hp_dev,
+               cudaStream_t stream);
+int tfop_zero(void* p, size_t bytes, cudaStream_t stream);
+
+/* ---- multi-tensor gradient pack (csrc/pack.cu) ---------------------------
+ * The "pack gradients into few tensors" step before the collective in
+ * keras-API/multi_worker_strategy-with-keras.py:76-77. nseg <= 128. */
+typedef struct tfop_pack_seg {
+    const void* src;
+    unsigned long long dst_off; /* element offset in dst, multiple of 8 */
+    unsigned long long n;       /* elements */
+} tfop_pack_seg;
+int tfop_multi_pack_bf16(const tfop_pack_seg* segs, int nseg, int src_dtype, void* dst,
+                         float scale, cudaStream_t stream);
+
+/* ---- input pipeline tail (csrc/preproc.cu) -------------------------------
+ * Per-step feed of examples/v1/dist-mnist/dist_mnist.py:275-281. */
+int tfop_u8_to_bf16_normalize(const void* in_u8, void* out_bf16, size_t n, int channels,
+                              const float* mean, const float* stdv, cudaStream_t stream);
+
+/* ---- fused BatchNorm / ReLU / residual, NHWC bf16 (csrc/bn.cu) -----------
+ * No reference counterpart (the reference ships no kernels); compute side of
+ * the PyTorchJob ResNet-50 config. `workspace` = tfop_bn_workspace_bytes()
+ * bytes of zero-initialised device memory, reusable across layers on one
+ * stream. */
+size_t tfop_bn_workspace_bytes(void);
+int tfop_bn_fwd_stats(const void* x, size_t M, int C, const void* gamma, const void* beta,
+                      int param_dtype, float* running_mean, float* running_var, float momentum,
+                      float eps, float* scale_shift, float* save_mean, float* save_invstd,
+                      void* workspace, cudaStream_t stream);
+int tfop_bn_fwd_apply(const void* x, const void* res, void* y, void* mask,
+                      const float* scale_shift, size_t M, int C, int relu, cudaStream_t stream);
+int tfop_bn_bwd_reduce(const void* dy, const void* x, const void* mask, const float* save_mean,
+                       const float* save_invstd, size_t M, int C, void* dgamma, void* dbeta,
+                       int param_dtype, float* coef, void* workspace, cudaStream_t stream);
+int tfop_bn_bwd_apply(const void* dy, const void* x, const void* mask, const float* save_mean,
+                      const float* save_invstd, const void* gamma, int param_dtype,
+                      const float* coef, void* dx, void* dres, size_t M, int C,
+                      cudaStream_t stream);
+
+/* ---- K7: tcgen05 / TMEM / TMA bf16 GEMM (csrc/gemm_tcgen05.cu) -----------
+ * C[M,N] = epi(A[M,K] * B[N,K]^T + bias); the dense layers of
+ * examples/v1/dist-mnist/dist_mnist.py:188-192. epilogue: 0 none, 1 bias,
+ * 2 bias+GeLU(erf), 3 bias+ReLU, 4 bias+GeLU(tanh). tile_n: 0 auto/128/256. */
+int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias, int bias_dtype,
+                      int M, int N, int K, int lda, int ldb, int ldc, int out_dtype,
+                      int epilogue, int tile_n, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFOP_B200_H_ */

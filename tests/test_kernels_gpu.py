@@ -1,0 +1,196 @@
+"""Numerics of the hand-written sm_100a kernels against plain PyTorch fp32 references."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from tf_operator_b200.ops import _lib
+    _lib.load()  # fails loudly if libtfop_b200.so is missing
+    return torch.device("cuda", 0)
+
+
+# ----------------------------------------------------------------------------- BN
+@pytest.mark.parametrize("shape", [(8, 64, 14, 14), (4, 256, 7, 9), (2, 2048, 3, 3), (16, 128, 28, 28)])
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False), (False, True)])
+def test_fused_bn_matches_fp32_reference(dev, shape, relu, res):
+    from tf_operator_b200.ops.bn import fused_bn_act
+    torch.manual_seed(0)
+    n, c, h, w = shape
+    x = (torch.randn(shape, device=dev) * 1.5 + 0.3).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True)
+    r = torch.randn(shape, device=dev).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True) if res else None
+    gamma = (torch.rand(c, device=dev) + 0.5).to(torch.bfloat16).requires_grad_(True)
+    beta = (torch.randn(c, device=dev) * 0.2).to(torch.bfloat16).requires_grad_(True)
+    rm = torch.zeros(c, device=dev)
+    rv = torch.ones(c, device=dev)
+    y = fused_bn_act(x, gamma, beta, rm, rv, True, 0.1, 1e-5, relu, r)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+
+    # fp32 reference of the same op
+    xr = x.detach().float().requires_grad_(True)
+    rr = r.detach().float().requires_grad_(True) if res else None
+    gr = gamma.detach().float().requires_grad_(True)
+    br = beta.detach().float().requires_grad_(True)
+    rm2 = torch.zeros(c, device=dev)
+    rv2 = torch.ones(c, device=dev)
+    yr = F.batch_norm(xr, rm2, rv2, gr, br, True, 0.1, 1e-5)
+    if res:
+        yr = yr + rr
+    if relu:
+        yr = F.relu(yr)
+    yr.backward(dy.float())
+
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(rm, rm2, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(rv, rv2, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=3e-2, atol=3e-2)
+    if res:
+        torch.testing.assert_close(r.grad.float(), rr.grad, rtol=2e-2, atol=2e-2)
+    m = n * h * w
+    tol = 2e-2 * math.sqrt(m) + 0.05
+    torch.testing.assert_close(gamma.grad.float(), gr.grad, rtol=3e-2, atol=tol)
+    torch.testing.assert_close(beta.grad.float(), br.grad, rtol=3e-2, atol=tol)
+
+
+def test_fused_bn_eval_mode(dev):
+    from tf_operator_b200.ops.bn import fused_bn_act
+    x = torch.randn(4, 64, 8, 8, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    g = torch.rand(64, device=dev) + 0.5
+    b = torch.randn(64, device=dev)
+    rm, rv = torch.randn(64, device=dev) * 0.1, torch.rand(64, device=dev) + 0.5
+    y = fused_bn_act(x, g, b, rm, rv, False, 0.1, 1e-5, True, None)
+    yr = F.relu(F.batch_norm(x.float(), rm, rv, g, b, False, 0.1, 1e-5))
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=2e-2)
+
+
+# ----------------------------------------------------------------------------- optimizers
+@pytest.mark.parametrize("grad_dtype", [torch.bfloat16, torch.float32])
+def test_fused_sgd_momentum(dev, grad_dtype):
+    from tf_operator_b200.ops import optim as fo
+    n, n_decay = 8 * 1000 + 64, 8 * 700
+    torch.manual_seed(1)
+    master = torch.randn(n, device=dev)
+    mom = torch.randn(n, device=dev) * 0.1
+    grad = torch.randn(n, device=dev).to(grad_dtype)
+    w16 = torch.zeros(n, device=dev, dtype=torch.bfloat16)
+    lr, mu, wd = 0.1, 0.9, 1e-2
+    hp = torch.tensor([lr, mu, wd, 1.0, 0.9, 0.999, 1e-8, 1.0], device=dev)
+    m_ref, v_ref = master.clone(), mom.clone()
+    g = grad.float().clone()
+    g[:n_decay] += wd * m_ref[:n_decay]
+    v_ref = mu * v_ref + g
+    m_ref = m_ref - lr * v_ref
+    fo.sgd_momentum_(master, mom, grad, w16, n_decay, hp)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(master, m_ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(mom, v_ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(w16.float(), m_ref, rtol=1e-2, atol=1e-2)
+
+
+def test_fused_adamw(dev):
+    from tf_operator_b200.ops import optim as fo
+    n = 8 * 512
+    torch.manual_seed(2)
+    p = torch.nn.Parameter(torch.randn(n, device=dev))
+    master = p.detach().clone()
+    m1, m2 = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    w16 = torch.zeros(n, device=dev, dtype=torch.bfloat16)
+    ref = torch.optim.AdamW([p], lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01)
+    for step in range(1, 4):
+        g = torch.randn(n, device=dev)
+        p.grad = g.clone()
+        ref.step()
+        hp = torch.tensor([1e-2, 0.0, 0.01, 1.0, 0.9, 0.999, 1e-8, float(step)], device=dev)
+        fo.adamw_(master, m1, m2, g, w16, n, hp)
+    torch.testing.assert_close(master, p.detach(), rtol=1e-4, atol=1e-5)
+
+
+def test_multi_pack_and_preproc(dev):
+    from tf_operator_b200.ops import optim as fo, preproc
+    torch.manual_seed(3)
+    sizes = [5, 64, 1000, 8, 33] * 30  # 150 tensors -> two launches
+    srcs = [torch.randn(s, device=dev) for s in sizes]
+    offs, off = [], 0
+    for s in sizes:
+        offs.append(off)
+        off += (s + 7) // 8 * 8
+    dst = torch.zeros(off, device=dev, dtype=torch.bfloat16)
+    fo.multi_pack_bf16(srcs, offs, dst, 0.5)
+    for t, o in zip(srcs, offs):
+        torch.testing.assert_close(dst[o:o + t.numel()].float(), (t * 0.5).bfloat16().float())
+    srcs16 = [t.bfloat16() for t in srcs]
+    dst.zero_()
+    fo.multi_pack_bf16(srcs16, offs, dst, 1.0)
+    for t, o in zip(srcs16, offs):
+        assert torch.equal(dst[o:o + t.numel()], t)
+
+    x = torch.randint(0, 256, (3, 17, 19, 3), dtype=torch.uint8, device=dev)
+    y = preproc.u8_to_bf16_normalize(x)
+    mean = torch.tensor(preproc.IMAGENET_MEAN, device=dev)
+    std = torch.tensor(preproc.IMAGENET_STD, device=dev)
+    ref = ((x.float() / 255 - mean) / std).permute(0, 3, 1, 2)
+    assert y.shape == (3, 3, 17, 19)
+    torch.testing.assert_close(y.float(), ref, rtol=1e-2, atol=1e-2)
+
+
+# ----------------------------------------------------------------------------- all-reduce (emulated ranks, one GPU)
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("algo", [1, 2])
+@pytest.mark.parametrize("wire,in_dt,out_dt", [
+    (torch.bfloat16, torch.float32, torch.float32),
+    (torch.bfloat16, torch.bfloat16, torch.bfloat16),
+    (torch.float32, torch.float32, torch.float32),
+])
+@pytest.mark.parametrize("n", [1000, 256 * 500 * 2])
+def test_allreduce_emulated_matches_sum(dev, world, algo, wire, in_dt, out_dt, n):
+    from tf_operator_b200.runtime.symm import SymmetricComm, all_reduce_emulated
+    torch.manual_seed(4)
+    comms = SymmetricComm.emulated(world, 4 << 20)
+    try:
+        ins = [(torch.randn(n, device=dev)).to(in_dt) for _ in range(world)]
+        outs = [torch.zeros(n, device=dev, dtype=out_dt) for _ in range(world)]
+        scale = 1.0 / world
+        for _ in range(3):  # repeated calls exercise the generation counters / parity buffers
+            all_reduce_emulated(comms, n, inps=ins, outs=outs, wire_dtype=wire, scale=scale, algo=algo)
+        torch.cuda.synchronize()
+        assert not comms[0].check_error()
+        wire_in = [t.to(wire).float() for t in ins]
+        ref = sum(wire_in) * scale
+        if algo == 2:
+            ref = ref.to(wire).float()
+        tol = 2e-2 if (wire == torch.bfloat16 or out_dt == torch.bfloat16) else 1e-5
+        for o in outs:
+            torch.testing.assert_close(o.float(), ref, rtol=tol, atol=tol)
+        for o in outs[1:]:
+            assert torch.equal(o, outs[0]), "all ranks must get bitwise-identical results"
+    finally:
+        for c in comms:
+            c.close()
+
+
+def test_allreduce_emulated_in_place_two_shot(dev):
+    """Gradient-bucket mode: data lives in symmetric memory, reduced in place."""
+    from tf_operator_b200.runtime.symm import SymmetricComm, all_reduce_emulated, TWO_SHOT
+    world, n, off = 4, 100_000, 4096
+    comms = SymmetricComm.emulated(world, 1 << 20)
+    try:
+        vals = [torch.randn(n, device=dev).bfloat16() for _ in range(world)]
+        for c, v in zip(comms, vals):
+            c.view(off, n, torch.bfloat16).copy_(v)
+        all_reduce_emulated(comms, n, sym_off=off, scale=0.25, algo=TWO_SHOT)
+        torch.cuda.synchronize()
+        ref = (sum(v.float() for v in vals) * 0.25).bfloat16()
+        for c in comms:
+            torch.testing.assert_close(c.view(off, n, torch.bfloat16).float(), ref.float(),
+                                       rtol=1e-2, atol=1e-2)
+    finally:
+        for c in comms:
+            c.close()

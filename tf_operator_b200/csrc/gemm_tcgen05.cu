@@ -1,0 +1,437 @@
+// K7: bf16 GEMM on the 5th-gen tensor cores, written directly against the
+// sm_100a ISA: TMA (cp.async.bulk.tensor) loads into 128B-swizzled shared
+// memory, tcgen05.mma issued by one elected thread, fp32 accumulators in TMEM
+// (double buffered so the epilogue of tile i overlaps the MMAs of tile i+1),
+// tcgen05.ld for the fused bias / GeLU / ReLU epilogue.
+//
+//   C[M,N] = act(A[M,K] * B[N,K]^T + bias[N])        ("TN": both K-major, i.e.
+//   torch.nn.functional.linear(x, W, b))
+//
+// Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer,
+// warp 2 = TMEM allocator, warps 4..7 = epilogue (one per 32 TMEM lanes).
+//
+// Reference parity: the dense layers of the example trainers
+// (examples/v1/dist-mnist/dist_mnist.py:188-192 matmuls -> cuBLAS/Eigen in the
+// reference stack); BASELINE.json requires the GEMMs on the named paths to be
+// tcgen05/TMEM/TMA kernels rather than library calls.
+#include "common.cuh"
+
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
+constexpr int UMMA_K = 16;
+constexpr int kNumThreads = 256;
+constexpr int kEpiWarp0 = 4;
+
+template <int BN>
+struct Cfg {
+    static constexpr int kStages = BN == 256 ? 4 : 6;
+    static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
+    static constexpr int kBBytes = BN * BLOCK_K * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
+    static constexpr int kBarBytes = 256;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + align slack
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst,
+                                            int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+            smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// K-major operand tile in SWIZZLE_128B layout: rows of 128 bytes, 8-row groups
+// 1024 bytes apart (SBO), LBO unused for swizzled K-major.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;             // LBO (ignored for 128B swizzle, K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;   // SBO
+    d |= (uint64_t)1 << 46;             // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;             // SWIZZLE_128B
+    return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major.
+__device__ __forceinline__ uint32_t make_idesc(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+          "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]),
+          "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]),
+          "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ float gelu_tanh(float x) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    const float u = k0 * x * fmaf(k1 * x, x, 1.f);
+    return 0.5f * x * (1.f + tanhf(u));
+}
+__device__ __forceinline__ float gelu_erf(float x) {
+    return 0.5f * x * (1.f + erff(x * 0.70710678118654752f));
+}
+
+enum { EPI_NONE = 0, EPI_BIAS = 1, EPI_BIAS_GELU = 2, EPI_BIAS_RELU = 3, EPI_BIAS_GELU_TANH = 4 };
+
+template <int BN>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
+               int K, int ldc, int out_dtype, int epi) {
+    using cfg = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    // 128B swizzle atoms need 1024-byte aligned tiles
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + cfg::kStages * cfg::kABytes;
+    uint64_t* bars = (uint64_t*)(smem + cfg::kStages * cfg::kStageBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + cfg::kStages;
+    uint64_t* tmem_full = bars + 2 * cfg::kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int m_blocks = (M + BLOCK_M - 1) / BLOCK_M;
+    const int n_blocks = (N + BN - 1) / BN;
+    const int num_tiles = m_blocks * n_blocks;
+    const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < cfg::kStages; ++i) {
+            mbar_init(&full[i], 1);
+            mbar_init(&empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         smem_u32(tmem_slot)),
+                     "r"((uint32_t)cfg::kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m0 = (t / n_blocks) * BLOCK_M;
+                const int n0 = (t % n_blocks) * BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_expect_tx(&full[stage], cfg::kStageBytes);
+                    tma_load_2d(&map_a, &full[stage], smem_a + stage * cfg::kABytes, kb * BLOCK_K,
+                                m0);
+                    tma_load_2d(&map_b, &full[stage], smem_b + stage * cfg::kBBytes, kb * BLOCK_K,
+                                n0);
+                    if (++stage == cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc(BLOCK_M, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tcgen05_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t a_addr = smem_u32(smem_a + stage * cfg::kABytes);
+                    const uint32_t b_addr = smem_u32(smem_b + stage * cfg::kBBytes);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        const uint64_t adesc = make_smem_desc(a_addr + k * UMMA_K * 2);
+                        const uint64_t bdesc = make_smem_desc(b_addr + k * UMMA_K * 2);
+                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty[stage]);  // frees the smem slot when the MMAs retire
+                    if (++stage == cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(&tmem_full[acc]);  // accumulator ready for the epilogue
+                if (++acc == 2) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===================== epilogue =====================
+        const int ew = warp - kEpiWarp0;  // == warp % 4: TMEM lane quadrant
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const int m0 = (t / n_blocks) * BLOCK_M;
+            const int n0 = (t % n_blocks) * BN;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tcgen05_fence_after();
+            const int row = m0 + ew * 32 + lane;
+            const uint32_t taddr = tmem_base + (uint32_t)(acc * BN) + ((uint32_t)(ew * 32) << 16);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + (uint32_t)c, r);
+                tmem_ld_wait();
+                const int col0 = n0 + c;
+                if (row < M && col0 < N) {
+                    float f[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(r[j]);
+                    if (epi != EPI_NONE) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int col = col0 + j;
+                            float bv = 0.f;
+                            if (col < N)
+                                bv = bias_dtype == TFOP_F32
+                                         ? ((const float*)bias)[col]
+                                         : __bfloat162float(((const __nv_bfloat16*)bias)[col]);
+                            float v = f[j] + bv;
+                            if (epi == EPI_BIAS_GELU)
+                                v = gelu_erf(v);
+                            else if (epi == EPI_BIAS_GELU_TANH)
+                                v = gelu_tanh(v);
+                            else if (epi == EPI_BIAS_RELU)
+                                v = fmaxf(v, 0.f);
+                            f[j] = v;
+                        }
+                    }
+                    if (out_dtype == TFOP_BF16) {
+                        __nv_bfloat16* crow = (__nv_bfloat16*)C + (size_t)row * ldc + col0;
+                        if (col0 + 32 <= N && (((uintptr_t)crow) & 15) == 0) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 8) {
+                                bf16x8 pk = f32_to_bf16x8(f + j);
+                                *reinterpret_cast<uint4*>(crow + j) = *reinterpret_cast<uint4*>(&pk);
+                            }
+                        } else {
+                            for (int j = 0; j < 32 && col0 + j < N; ++j)
+                                crow[j] = __float2bfloat16_rn(f[j]);
+                        }
+                    } else {
+                        float* crow = (float*)C + (size_t)row * ldc + col0;
+                        if (col0 + 32 <= N && (((uintptr_t)crow) & 15) == 0) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4)
+                                *reinterpret_cast<float4*>(crow + j) =
+                                    make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+                        } else {
+                            for (int j = 0; j < 32 && col0 + j < N; ++j) crow[j] = f[j];
+                        }
+                    }
+                }
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (++acc == 2) {
+                acc = 0;
+                acc_phase ^= 1;
+            }
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                     "r"((uint32_t)cfg::kTmemCols)
+                     : "memory");
+    }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+
+int get_encode() {
+    if (g_encode) return 0;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    TFOP_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    TFOP_REQUIRE(qres == cudaDriverEntryPointSuccess && fn != nullptr,
+                 "cuTensorMapEncodeTiled not available from the driver");
+    g_encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+    return 0;
+}
+
+// 2D bf16 row-major [rows, K] (ld elements between rows), box = [box_rows, 64] with 128B swizzle
+int make_map(CUtensorMap* map, const void* base, int rows, int K, int ld, int box_rows) {
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                          strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char msg[96];
+        snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+        tfop_set_error(__FILE__, __LINE__, msg);
+        return -1;
+    }
+    return 0;
+}
+
+int g_num_sms = 0;
+
+template <int BN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, void* C, const void* bias,
+           int bias_dtype, int M, int N, int K, int ldc, int out_dtype, int epi,
+           cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        TFOP_CUDA(cudaFuncSetAttribute(gemm_tn_kernel<BN>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<BN>::kSmemBytes));
+        attr_set = true;
+    }
+    const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
+    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    gemm_tn_kernel<BN><<<grid, kNumThreads, Cfg<BN>::kSmemBytes, stream>>>(
+        ma, mb, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epi);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+// C[M,N] = epi(A[M,K] * B[N,K]^T + bias[N]); A, B bf16 row-major with leading
+// dimensions lda/ldb (elements, multiples of 8; base pointers 16-byte aligned).
+// out_dtype: TFOP_BF16 or TFOP_F32. epilogue: 0 none, 1 +bias, 2 +bias,GeLU(erf),
+// 3 +bias,ReLU, 4 +bias,GeLU(tanh). tile_n: 0 auto, 128 or 256.
+TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias,
+                               int bias_dtype, int M, int N, int K, int lda, int ldb, int ldc,
+                               int out_dtype, int epilogue, int tile_n, cudaStream_t stream) {
+    TFOP_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
+    TFOP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "lda/ldb must be multiples of 8 elements (TMA)");
+    TFOP_REQUIRE((((uintptr_t)A) & 15) == 0 && (((uintptr_t)B) & 15) == 0,
+                 "A and B must be 16-byte aligned");
+    TFOP_REQUIRE(out_dtype == TFOP_BF16 || out_dtype == TFOP_F32, "bad out dtype");
+    TFOP_REQUIRE(epilogue >= 0 && epilogue <= 4, "bad epilogue");
+    TFOP_REQUIRE(epilogue == 0 || bias != nullptr, "epilogue needs a bias pointer");
+    if (get_encode() != 0) return -1;
+    if (g_num_sms == 0) {
+        int dev = 0;
+        TFOP_CUDA(cudaGetDevice(&dev));
+        TFOP_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    if (tile_n == 0) {
+        // wide tiles when they still fill the machine
+        const long tiles256 = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + 255) / 256);
+        tile_n = (N >= 256 && tiles256 >= g_num_sms) ? 256 : 128;
+    }
+    TFOP_REQUIRE(tile_n == 128 || tile_n == 256, "tile_n must be 0, 128 or 256");
+    CUtensorMap ma, mb;
+    if (make_map(&ma, A, M, K, lda, BLOCK_M) != 0) return -1;
+    if (make_map(&mb, B, N, K, ldb, tile_n) != 0) return -1;
+    if (tile_n == 256)
+        return launch<256>(ma, mb, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, stream);
+    return launch<128>(ma, mb, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, stream);
+}

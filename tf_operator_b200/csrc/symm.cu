@@ -1,0 +1,131 @@
+// Symmetric peer memory ("the Service DNS name becomes a peer-memory handle").
+//
+// One tfop_comm per replica process (one process per B200). Each rank owns a
+// data buffer and a signal pad allocated with cudaMalloc; the 64-byte CUDA IPC
+// handles of both are published through the launcher's rendezvous store (or
+// any byte transport) and opened by every peer, after which kernels read and
+// write peer HBM directly over NVLink 5 / NVSwitch.
+//
+// Reference parity: the reference operator only hands out DNS names + ports
+// (pkg/controller.v1/pytorch/pytorch.go:13-68); the transport lived in user
+// images. This file is the B200-native replacement for that transport's
+// address exchange.
+#include "common.cuh"
+#include "comm.h"
+
+#include <mutex>
+#include <new>
+
+static thread_local char g_err[512] = "";
+
+void tfop_set_error(const char* file, int line, const char* msg) {
+    snprintf(g_err, sizeof(g_err), "%s:%d: %s", file, line, msg);
+}
+
+TFOP_API const char* tfop_last_error(void) { return g_err; }
+
+TFOP_API int tfop_version(void) { return 100; }
+
+TFOP_API int tfop_comm_handle_bytes(void) { return (int)(2 * sizeof(cudaIpcMemHandle_t)); }
+
+static int comm_alloc_local(tfop_comm* c) {
+    // 2 MiB-align the data buffer size so the mapping granularity is friendly.
+    TFOP_CUDA(cudaMalloc(&c->data[c->rank], c->data_bytes));
+    TFOP_CUDA(cudaMemset(c->data[c->rank], 0, c->data_bytes));
+    void* sig = nullptr;
+    TFOP_CUDA(cudaMalloc(&sig, TFOP_SIG_BYTES));
+    TFOP_CUDA(cudaMemset(sig, 0, TFOP_SIG_BYTES));
+    c->sig[c->rank] = (uint32_t*)sig;
+    TFOP_CUDA(cudaMalloc((void**)&c->counters, TFOP_MAX_BLOCKS * sizeof(uint32_t)));
+    TFOP_CUDA(cudaMemset(c->counters, 0, TFOP_MAX_BLOCKS * sizeof(uint32_t)));
+    TFOP_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+
+TFOP_API int tfop_comm_create(int rank, int world, size_t data_bytes, tfop_comm** out) {
+    TFOP_REQUIRE(world >= 1 && world <= TFOP_MAX_WORLD, "world must be in [1, 8]");
+    TFOP_REQUIRE(rank >= 0 && rank < world, "rank out of range");
+    tfop_comm* c = new (std::nothrow) tfop_comm();
+    TFOP_REQUIRE(c != nullptr, "out of host memory");
+    memset(c, 0, sizeof(*c));
+    c->rank = rank;
+    c->world = world;
+    c->data_bytes = (data_bytes + 255) & ~size_t(255);
+    TFOP_CUDA(cudaGetDevice(&c->device));
+    int rc = comm_alloc_local(c);
+    if (rc != 0) {
+        delete c;
+        return rc;
+    }
+    *out = c;
+    return 0;
+}
+
+TFOP_API int tfop_comm_get_handle(tfop_comm* c, void* out_bytes) {
+    cudaIpcMemHandle_t h[2];
+    TFOP_CUDA(cudaIpcGetMemHandle(&h[0], c->data[c->rank]));
+    TFOP_CUDA(cudaIpcGetMemHandle(&h[1], (void*)c->sig[c->rank]));
+    memcpy(out_bytes, h, sizeof(h));
+    return 0;
+}
+
+// all_handles: world * tfop_comm_handle_bytes() bytes, rank-major.
+TFOP_API int tfop_comm_open_peers(tfop_comm* c, const void* all_handles) {
+    const cudaIpcMemHandle_t* h = (const cudaIpcMemHandle_t*)all_handles;
+    for (int p = 0; p < c->world; ++p) {
+        if (p == c->rank) continue;
+        void* d = nullptr;
+        void* s = nullptr;
+        TFOP_CUDA(cudaIpcOpenMemHandle(&d, h[2 * p], cudaIpcMemLazyEnablePeerAccess));
+        TFOP_CUDA(cudaIpcOpenMemHandle(&s, h[2 * p + 1], cudaIpcMemLazyEnablePeerAccess));
+        c->data[p] = d;
+        c->sig[p] = (uint32_t*)s;
+        c->opened[p] = 1;
+    }
+    return 0;
+}
+
+// Single-process, single-GPU emulation: `world` comm objects whose peer
+// tables point at each other's local allocations. Used by the GPU tests (a
+// multi-rank kernel is then run as ONE cooperative launch, never as kernels
+// that wait on each other across launches).
+TFOP_API int tfop_comm_create_emulated(int world, size_t data_bytes, tfop_comm** out) {
+    TFOP_REQUIRE(world >= 1 && world <= TFOP_MAX_WORLD, "world must be in [1, 8]");
+    for (int r = 0; r < world; ++r) {
+        int rc = tfop_comm_create(r, world, data_bytes, &out[r]);
+        if (rc != 0) return rc;
+        out[r]->emulated = 1;
+    }
+    for (int r = 0; r < world; ++r)
+        for (int p = 0; p < world; ++p) {
+            out[r]->data[p] = out[p]->data[p];
+            out[r]->sig[p] = out[p]->sig[p];
+        }
+    return 0;
+}
+
+TFOP_API void* tfop_comm_buffer(tfop_comm* c, int peer) {
+    if (peer < 0 || peer >= c->world) return nullptr;
+    return c->data[peer];
+}
+
+TFOP_API size_t tfop_comm_buffer_bytes(tfop_comm* c) { return c->data_bytes; }
+TFOP_API int tfop_comm_rank(tfop_comm* c) { return c->rank; }
+TFOP_API int tfop_comm_world(tfop_comm* c) { return c->world; }
+
+TFOP_API int tfop_comm_destroy(tfop_comm* c) {
+    if (!c) return 0;
+    cudaDeviceSynchronize();
+    for (int p = 0; p < c->world; ++p) {
+        if (p == c->rank) continue;
+        if (c->opened[p]) {
+            cudaIpcCloseMemHandle(c->data[p]);
+            cudaIpcCloseMemHandle((void*)c->sig[p]);
+        }
+    }
+    cudaFree(c->data[c->rank]);
+    cudaFree((void*)c->sig[c->rank]);
+    cudaFree((void*)c->counters);
+    delete c;
+    return 0;
+}

@@ -1,0 +1,121 @@
+"""ResNet family (18/34/50/101/152) for the PyTorchJob ResNet-50 DDP config
+(BASELINE.json config 2). Convolutions are cuDNN (a plain library op); every
+BatchNorm+ReLU(+residual add) goes through the fused NHWC kernels in
+ops/bn.py. ``fused=False`` builds the same network from stock torch modules and
+is the "reference mode" compute graph for the measured NCCL baseline
+(BASELINE.md section 3). The reference itself has no model code; its CNN example is
+examples/v1/distribution_strategy/keras-API/multi_worker_strategy-with-keras.py:42-60.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops.bn import FusedBatchNorm2d
+
+
+class _StockBNAct(nn.Module):
+    def __init__(self, c, relu=True, zero_init=False):
+        super().__init__()
+        self.bn = nn.BatchNorm2d(c)
+        if zero_init:
+            nn.init.zeros_(self.bn.weight)
+        self.relu = relu
+
+    def forward(self, x, residual=None):
+        y = self.bn(x)
+        if residual is not None:
+            y = y + residual
+        return F.relu(y, inplace=True) if self.relu else y
+
+
+def _bn(c, relu=True, fused=True, zero_init=False):
+    return FusedBatchNorm2d(c, relu=relu, zero_init=zero_init) if fused \
+        else _StockBNAct(c, relu, zero_init)
+
+
+def _conv(cin, cout, k, stride=1):
+    return nn.Conv2d(cin, cout, k, stride=stride, padding=k // 2, bias=False)
+
+
+class Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, cin, width, stride, fused, zero_init_residual):
+        super().__init__()
+        cout = width * self.expansion
+        self.conv1, self.bn1 = _conv(cin, width, 1), _bn(width, True, fused)
+        self.conv2, self.bn2 = _conv(width, width, 3, stride), _bn(width, True, fused)
+        self.conv3 = _conv(width, cout, 1)
+        self.bn3 = _bn(cout, True, fused, zero_init=zero_init_residual)
+        self.down = None
+        if stride != 1 or cin != cout:
+            self.down = nn.ModuleList([_conv(cin, cout, 1, stride), _bn(cout, False, fused)])
+
+    def forward(self, x):
+        idt = x if self.down is None else self.down[1](self.down[0](x))
+        y = self.bn1(self.conv1(x))
+        y = self.bn2(self.conv2(y))
+        return self.bn3(self.conv3(y), idt)
+
+
+class BasicBlock(nn.Module):
+    expansion = 1
+
+    def __init__(self, cin, width, stride, fused, zero_init_residual):
+        super().__init__()
+        self.conv1, self.bn1 = _conv(cin, width, 3, stride), _bn(width, True, fused)
+        self.conv2 = _conv(width, width, 3)
+        self.bn2 = _bn(width, True, fused, zero_init=zero_init_residual)
+        self.down = None
+        if stride != 1 or cin != width:
+            self.down = nn.ModuleList([_conv(cin, width, 1, stride), _bn(width, False, fused)])
+
+    def forward(self, x):
+        idt = x if self.down is None else self.down[1](self.down[0](x))
+        y = self.bn1(self.conv1(x))
+        return self.bn2(self.conv2(y), idt)
+
+
+_CFG = {
+    18: (BasicBlock, (2, 2, 2, 2)), 34: (BasicBlock, (3, 4, 6, 3)),
+    50: (Bottleneck, (3, 4, 6, 3)), 101: (Bottleneck, (3, 4, 23, 3)),
+    152: (Bottleneck, (3, 8, 36, 3)),
+}
+
+
+class ResNet(nn.Module):
+    def __init__(self, depth: int = 50, num_classes: int = 1000, fused: bool = True,
+                 zero_init_residual: bool = True, width: int = 64):
+        super().__init__()
+        block, layers = _CFG[depth]
+        self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
+        self.bn1 = _bn(width, True, fused)
+        self.pool = nn.MaxPool2d(3, stride=2, padding=1)
+        stages, cin = [], width
+        for i, nblk in enumerate(layers):
+            w = width * (2 ** i)
+            for j in range(nblk):
+                stages.append(block(cin, w, (2 if i > 0 and j == 0 else 1), fused,
+                                    zero_init_residual))
+                cin = w * block.expansion
+        self.blocks = nn.Sequential(*stages)
+        self.fc = nn.Linear(cin, num_classes)
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+
+    def forward(self, x):
+        x = self.pool(self.bn1(self.conv1(x)))
+        x = self.blocks(x)
+        x = F.adaptive_avg_pool2d(x, 1).flatten(1)
+        return self.fc(x)
+
+
+def resnet50(**kw) -> ResNet:
+    return ResNet(50, **kw)
+
+
+def resnet18(**kw) -> ResNet:
+    return ResNet(18, **kw)

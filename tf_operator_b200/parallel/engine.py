@@ -1,0 +1,238 @@
+"""Data-parallel training engine (K3): the replica-side loop of a PyTorchJob.
+
+    engine = DataParallelEngine(model, comm=SymmetricComm|None, lr=..., ...)
+    handle = engine.step(images_u8_pinned, labels_pinned)   # H2D + fwd + bwd + comm + opt
+    loss = handle.result()                                   # D2H read
+
+One step is: async H2D of the uint8 batch (copy stream, double-buffered
+staging) -> fused u8->bf16 normalise -> forward/backward (cuDNN convs + fused
+BN kernels) -> per-bucket multi-tensor pack into symmetric memory and in-place
+fused P2P all-reduce on a side stream as the bucket's gradients become ready
+(overlapping the rest of backward) -> one fused SGD kernel over the flat
+buffers. With ``graph=True`` everything after the H2D copy is one CUDA graph.
+
+Reference parity: the training loop of the reference's example workloads
+(examples/v1/distribution_strategy/keras-API/multi_worker_strategy-with-keras.py:
+106-120: strategy scope, compile, fit) whose gradient exchange is a NCCL
+library call; here it is the hand-written kernels of csrc/allreduce.cu.
+"""
+from __future__ import annotations
+
+import threading
+from typing import Callable, Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops import optim as fopt
+from ..ops import preproc
+from ..runtime.symm import SymmetricComm, TWO_SHOT
+from .flat import FlatParams
+
+
+class StepHandle:
+    """Result of an asynchronous step; ``result()`` is the device->host read."""
+
+    def __init__(self, host_loss: torch.Tensor, event: torch.cuda.Event):
+        self._host, self._event = host_loss, event
+
+    def result(self) -> float:
+        self._event.synchronize()
+        return float(self._host.item())
+
+
+class DataParallelEngine:
+    def __init__(self, model: nn.Module, *, comm: Optional[SymmetricComm] = None,
+                 batch_size: int, image_size: int = 224, channels: int = 3,
+                 lr: float = 0.1, momentum: float = 0.9, weight_decay: float = 1e-4,
+                 nesterov: bool = False, bucket_bytes: int = 16 << 20, graph: bool = True,
+                 overlap: bool = True, comm_blocks: int = 32,
+                 loss_fn: Optional[Callable] = None, device: Optional[torch.device] = None,
+                 label_smoothing: float = 0.0):
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.comm = comm
+        self.world = comm.world if comm is not None else 1
+        self.batch_size, self.image_size, self.channels = batch_size, image_size, channels
+        self.loss_fn = loss_fn or (lambda out, y: F.cross_entropy(
+            out.float(), y, label_smoothing=label_smoothing))
+        self.overlap = overlap and self.world > 1
+        self.comm_blocks = comm_blocks
+        self.kernel_launches_per_step = 0
+
+        model.to(self.device).to(memory_format=torch.channels_last)
+        self.model = model
+        grad_buf = None
+        total = sum((p.numel() + 7) // 8 * 8 for p in model.parameters() if p.requires_grad)
+        if comm is not None:
+            assert comm.nbytes >= total * 2, "symmetric buffer too small for the gradient bucket"
+            grad_buf = comm.view(0, total, torch.bfloat16)
+        self.flat = FlatParams(model, self.device, grad_buffer=grad_buf, bucket_bytes=bucket_bytes)
+        self.mom = torch.zeros(self.flat.total, dtype=torch.float32, device=self.device)
+        self.hp = torch.zeros(8, dtype=torch.float32, device=self.device)
+        self._hp_host = torch.tensor([lr, momentum, weight_decay, 1.0, 0.9, 0.999, 1e-8, 0.0],
+                                     dtype=torch.float32).pin_memory()
+        self.hp.copy_(self._hp_host)
+        self.nesterov = nesterov
+
+        # static device inputs / outputs (graph-friendly) + double-buffered staging
+        shp = (batch_size, image_size, image_size, channels)
+        self.x_u8 = torch.zeros(shp, dtype=torch.uint8, device=self.device)
+        self.x_bf16 = torch.zeros(shp, dtype=torch.bfloat16, device=self.device)
+        self.labels = torch.zeros(batch_size, dtype=torch.int64, device=self.device)
+        self.loss_dev = torch.zeros((), dtype=torch.float32, device=self.device)
+        self._stage_x = [torch.zeros_like(self.x_u8) for _ in range(2)]
+        self._stage_y = [torch.zeros_like(self.labels) for _ in range(2)]
+        self._stage_ready = [torch.cuda.Event() for _ in range(2)]
+        self._stage_free = [torch.cuda.Event() for _ in range(2)]
+        self._host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self._slot = 0
+        self._prefetched = None
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self.main_stream = torch.cuda.Stream(device=self.device)
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._use_graph = graph
+        self._steps = 0
+        self._hook_lock = threading.Lock()
+        self._install_hooks()
+
+    # ------------------------------------------------------------------ comm
+    def _install_hooks(self):
+        if self.world == 1:
+            return
+        for s in self.flat.slots:
+            s.param.register_post_accumulate_grad_hook(self._make_hook())
+
+    def _make_hook(self):
+        def hook(p):
+            if not self.overlap or not self._in_backward:
+                return
+            b = self.flat.bucket_of(p)
+            with self._hook_lock:
+                b.pending -= 1
+                fire = b.pending == 0
+            if fire:
+                cur = torch.cuda.current_stream()
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                self.comm_stream.wait_event(ev)
+                self._reduce_bucket(b, self.comm_stream)
+        return hook
+
+    def _reduce_bucket(self, b, stream):
+        srcs = [s.param.grad for s in b.slots]
+        offs = [s.offset for s in b.slots]
+        fopt.multi_pack_bf16(srcs, offs, self.flat.grads, 1.0, stream)
+        if self.world > 1:
+            # in place on the symmetric gradient bucket: sum over ranks * 1/world
+            self.comm.all_reduce(b.hi - b.lo, sym_off=b.lo * 2, wire_dtype=torch.bfloat16,
+                                 scale=1.0 / self.world, algo=TWO_SHOT,
+                                 max_blocks=self.comm_blocks, stream=stream)
+
+    # ------------------------------------------------------------------ step
+    _in_backward = False
+
+    def _body(self):
+        """fwd + bwd + gradient exchange + optimizer on the current stream."""
+        from ..ops import _lib
+        l0 = _lib.launches_total()
+        x = preproc.u8_to_bf16_normalize(self.x_u8, self.x_bf16)
+        for p in self.model.parameters():
+            p.grad = None
+        for b in self.flat.buckets:
+            b.pending = len(b.slots)
+        out = self.model(x)
+        loss = self.loss_fn(out, self.labels)
+        self.loss_dev.copy_(loss.detach())
+        self._in_backward = True
+        try:
+            loss.backward()
+        finally:
+            self._in_backward = False
+        cur = torch.cuda.current_stream()
+        if self.overlap:
+            cur.wait_stream(self.comm_stream)
+        else:
+            for b in self.flat.buckets:
+                self._reduce_bucket(b, cur)
+        fopt.sgd_momentum_(self.flat.master, self.mom, self.flat.grads, self.flat.weights,
+                           self.flat.n_decay, self.hp, self.nesterov, cur)
+        self.kernel_launches_per_step = _lib.launches_total() - l0
+        if self._steps == 0 and not torch.cuda.is_current_stream_capturing():
+            bad = self.flat.check_grad_layouts()
+            if bad:
+                raise RuntimeError(f"gradient layout differs from parameter layout for {bad[:4]}")
+
+    def _capture(self):
+        # warm-up on the main stream (cuDNN autotune, allocator), then capture once
+        with torch.cuda.stream(self.main_stream):
+            for _ in range(3):
+                self._body()
+        self.main_stream.synchronize()
+        if self.comm is not None:
+            torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=self.main_stream):
+            self._body()
+        self._graph = g
+
+    def run_device_step(self):
+        """One step on the already-resident device batch (no host traffic)."""
+        if self._use_graph:
+            if self._graph is None:
+                self._capture()
+            with torch.cuda.stream(self.main_stream):
+                self._graph.replay()
+        else:
+            with torch.cuda.stream(self.main_stream):
+                self._body()
+        self._steps += 1
+
+    def prefetch(self, images_u8: torch.Tensor, labels: torch.Tensor):
+        """Start the H2D copy of a (pinned) host batch into the free staging slot."""
+        slot = self._slot
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._stage_free[slot])
+            self._stage_x[slot].copy_(images_u8, non_blocking=True)
+            self._stage_y[slot].copy_(labels, non_blocking=True)
+            self._stage_ready[slot].record(self.copy_stream)
+        self._prefetched = slot
+        self._slot ^= 1
+
+    def step(self, images_u8: Optional[torch.Tensor] = None,
+             labels: Optional[torch.Tensor] = None) -> StepHandle:
+        """Full step. Pass a host batch, or nothing if ``prefetch`` was already called."""
+        if images_u8 is not None:
+            self.prefetch(images_u8, labels)
+        slot = self._prefetched
+        assert slot is not None, "step() needs a batch (argument or prefetch)"
+        self._prefetched = None
+        ms = self.main_stream
+        ms.wait_event(self._stage_ready[slot])
+        with torch.cuda.stream(ms):
+            self.x_u8.copy_(self._stage_x[slot], non_blocking=True)
+            self.labels.copy_(self._stage_y[slot], non_blocking=True)
+            self._stage_free[slot].record(ms)
+        self.run_device_step()
+        host = self._host_loss[self._steps & 1]
+        ev = torch.cuda.Event()
+        with torch.cuda.stream(ms):
+            host.copy_(self.loss_dev, non_blocking=True)
+            ev.record(ms)
+        return StepHandle(host, ev)
+
+    # ------------------------------------------------------------------ misc
+    def set_lr(self, lr: float):
+        self._hp_host[0] = lr
+        with torch.cuda.stream(self.main_stream):
+            self.hp.copy_(self._hp_host, non_blocking=True)
+
+    def h2d_bytes_per_step(self) -> int:
+        return self.x_u8.numel() + self.labels.numel() * 8
+
+    def d2h_bytes_per_step(self) -> int:
+        return 4
+
+    def synchronize(self):
+        torch.cuda.synchronize(self.device)

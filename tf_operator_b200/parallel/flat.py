@@ -1,0 +1,124 @@
+"""Flat parameter / gradient / optimizer-state buffers.
+
+Every parameter of the model becomes a strided view into one flat bf16 weight
+buffer; gradients are packed (cast fused) into one flat bf16 bucket buffer —
+placed in symmetric peer memory when a communicator is given, so the
+all-reduce runs on it in place with zero copies — and the optimizer is a single
+fused kernel over the flat fp32 master / state buffers.
+
+Layout: [ weight-decay params (reverse registration order) | no-decay params ],
+each slot padded to 8 elements (16 B in bf16). Reverse order means the slots
+fill front-to-back as backward proceeds, so buckets are contiguous ranges.
+
+Counterpart in the reference: none (the gradient exchange is a library call in
+examples/v1/distribution_strategy/keras-API/multi_worker_strategy-with-keras.py:76-77).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+@dataclass
+class Slot:
+    name: str
+    param: nn.Parameter
+    offset: int          # element offset into the flat buffers
+    numel: int
+    decay: bool
+
+
+@dataclass
+class Bucket:
+    lo: int              # element range [lo, hi) in the flat buffers
+    hi: int
+    slots: List[Slot] = field(default_factory=list)
+    pending: int = 0
+
+
+class FlatParams:
+    def __init__(self, model: nn.Module, device: torch.device, *, grad_buffer: Optional[torch.Tensor] = None,
+                 bucket_bytes: int = 16 << 20, weight_dtype: torch.dtype = torch.bfloat16):
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        decay = [(n, p) for n, p in named if p.ndim > 1]
+        nodecay = [(n, p) for n, p in named if p.ndim <= 1]
+        self.slots: List[Slot] = []
+        off = 0
+        for group, is_decay in ((decay[::-1], True), (nodecay[::-1], False)):
+            for n, p in group:
+                self.slots.append(Slot(n, p, off, p.numel(), is_decay))
+                off += _pad8(p.numel())
+            if is_decay:
+                self.n_decay = off
+        self.total = off
+        self.device = device
+        self.weight_dtype = weight_dtype
+        self.master = torch.zeros(self.total, dtype=torch.float32, device=device)
+        self.weights = torch.zeros(self.total, dtype=weight_dtype, device=device)
+        if grad_buffer is not None:
+            assert grad_buffer.numel() >= self.total and grad_buffer.dtype == torch.bfloat16
+            self.grads = grad_buffer[: self.total]
+        else:
+            self.grads = torch.zeros(self.total, dtype=torch.bfloat16, device=device)
+        # move parameter storage into the flat weight buffer, keeping each
+        # parameter's shape AND strides (channels-last conv weights stay channels-last)
+        with torch.no_grad():
+            for s in self.slots:
+                p = s.param
+                src = p.detach().to(device)
+                if not _is_dense(src):
+                    src = src.contiguous()
+                view = torch.as_strided(self.weights, src.shape, src.stride(), s.offset)
+                mview = torch.as_strided(self.master, src.shape, src.stride(), s.offset)
+                mview.copy_(src.float())
+                view.copy_(src.to(weight_dtype))
+                p.data = view
+        # buckets: contiguous ranges of the decay region + one for the no-decay tail
+        self.buckets: List[Bucket] = []
+        cur = None
+        limit = max(1, bucket_bytes // 2)
+        for s in self.slots:
+            if cur is None or (s.decay and cur.hi - cur.lo >= limit) or \
+                    (not s.decay and cur.slots and cur.slots[0].decay):
+                cur = Bucket(s.offset, s.offset)
+                self.buckets.append(cur)
+            cur.slots.append(s)
+            cur.hi = s.offset + _pad8(s.numel)
+        self._bucket_of = {}
+        for b in self.buckets:
+            for s in b.slots:
+                self._bucket_of[id(s.param)] = b
+
+    def bucket_of(self, p: nn.Parameter) -> Bucket:
+        return self._bucket_of[id(p)]
+
+    def grad_view(self, s: Slot) -> torch.Tensor:
+        p = s.param
+        return torch.as_strided(self.grads, p.shape, p.stride(), s.offset)
+
+    def check_grad_layouts(self) -> List[str]:
+        """Names of parameters whose .grad strides differ from the parameter's."""
+        def sig(t):
+            return [(sz, st) for sz, st in zip(t.shape, t.stride()) if sz > 1]
+        return [s.name for s in self.slots
+                if s.param.grad is not None and sig(s.param.grad) != sig(s.param)]
+
+
+def _is_dense(t: torch.Tensor) -> bool:
+    """True when the tensor covers numel() distinct consecutive elements."""
+    if t.numel() == 0:
+        return True
+    sizes_strides = sorted(((st, sz) for sz, st in zip(t.shape, t.stride()) if sz > 1))
+    expect = 1
+    for st, sz in sizes_strides:
+        if st != expect:
+            return False
+        expect *= sz
+    return True

@@ -1,0 +1,148 @@
+"""Symmetric peer memory + fused P2P all-reduce front-end (csrc/symm.cu, csrc/allreduce.cu).
+
+One ``SymmetricComm`` per replica process. Each rank allocates a data buffer and
+a signal pad, publishes their CUDA IPC handles through any byte-exchange
+callable (the launcher's rendezvous store, or torch.distributed), and maps all
+peers. After that, collectives are single kernels that read/write peer HBM over
+NVLink — NCCL is only the measured baseline.
+
+Replaces the DNS + TCP addressing the reference hands to the workload
+(pkg/controller.v1/pytorch/pytorch.go:13-68).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Callable, List, Optional, Sequence
+
+import torch
+
+from ..ops import _lib
+
+AUTO, ONE_SHOT, TWO_SHOT = 0, 1, 2
+
+
+class _RawCudaBuffer:
+    """Expose a raw device pointer to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self._owner = owner
+        self.__cuda_array_interface__ = {
+            "shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2,
+            "strides": None,
+        }
+
+
+def tensor_from_ptr(ptr: int, nbytes: int, device, owner=None) -> torch.Tensor:
+    return torch.as_tensor(_RawCudaBuffer(ptr, nbytes, owner), device=device)
+
+
+class SymmetricComm:
+    def __init__(self, handle: int, rank: int, world: int, device: torch.device,
+                 emulated: bool = False):
+        self._h = C.c_void_p(handle)
+        self.rank, self.world, self.device, self.emulated = rank, world, device, emulated
+        self._lib = _lib.load()
+        self.nbytes = self._lib.tfop_comm_buffer_bytes(self._h)
+        self._views = {}
+
+    # ---- construction ------------------------------------------------------
+    @classmethod
+    def create(cls, rank: int, world: int, nbytes: int,
+               exchange: Callable[[bytes], Sequence[bytes]],
+               device: Optional[torch.device] = None) -> "SymmetricComm":
+        """``exchange(my_bytes) -> [bytes of rank 0, ..., bytes of rank world-1]``."""
+        lib = _lib.load()
+        device = device or torch.device("cuda", torch.cuda.current_device())
+        with torch.cuda.device(device):
+            h = C.c_void_p()
+            _lib.check(lib.tfop_comm_create(rank, world, nbytes, C.byref(h)), "comm_create")
+            hb = lib.tfop_comm_handle_bytes()
+            mine = C.create_string_buffer(hb)
+            _lib.check(lib.tfop_comm_get_handle(h, mine), "comm_get_handle")
+            allh = exchange(mine.raw)
+            assert len(allh) == world and all(len(b) == hb for b in allh)
+            blob = C.create_string_buffer(b"".join(allh), hb * world)
+            if world > 1:
+                _lib.check(lib.tfop_comm_open_peers(h, blob), "comm_open_peers")
+        return cls(h.value, rank, world, device)
+
+    @classmethod
+    def from_torch_distributed(cls, nbytes: int, group=None) -> "SymmetricComm":
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+
+        def exchange(b: bytes):
+            out: List[Optional[bytes]] = [None] * world
+            dist.all_gather_object(out, b, group=group)
+            return out
+
+        comm = cls.create(rank, world, nbytes, exchange)
+        dist.barrier(group=group)
+        return comm
+
+    @classmethod
+    def emulated(cls, world: int, nbytes: int,
+                 device: Optional[torch.device] = None) -> List["SymmetricComm"]:
+        """All ranks on ONE GPU in ONE process (tests; single cooperative launches)."""
+        lib = _lib.load()
+        device = device or torch.device("cuda", torch.cuda.current_device())
+        arr = (C.c_void_p * world)()
+        with torch.cuda.device(device):
+            _lib.check(lib.tfop_comm_create_emulated(world, nbytes, arr), "comm_create_emulated")
+        return [cls(arr[r], r, world, device, emulated=True) for r in range(world)]
+
+    # ---- buffers -----------------------------------------------------------
+    def buffer(self, peer: Optional[int] = None) -> torch.Tensor:
+        """uint8 view of rank ``peer``'s symmetric buffer as mapped in this process."""
+        peer = self.rank if peer is None else peer
+        if peer not in self._views:
+            p = self._lib.tfop_comm_buffer(self._h, peer)
+            self._views[peer] = tensor_from_ptr(p, self.nbytes, self.device, owner=self)
+        return self._views[peer]
+
+    def view(self, byte_off: int, numel: int, dtype: torch.dtype,
+             peer: Optional[int] = None) -> torch.Tensor:
+        es = torch.empty((), dtype=dtype).element_size()
+        return self.buffer(peer)[byte_off:byte_off + numel * es].view(dtype)
+
+    # ---- collectives -------------------------------------------------------
+    def all_reduce(self, n: int, *, inp: Optional[torch.Tensor] = None,
+                   out: Optional[torch.Tensor] = None, sym_off: int = 0,
+                   wire_dtype: torch.dtype = torch.bfloat16, scale: float = 1.0,
+                   algo: int = AUTO, max_blocks: int = 0, stream=None) -> None:
+        """Fused sum-all-reduce * scale. ``inp=None``: data already in the symmetric buffer at
+        ``sym_off`` (wire dtype). ``out=None``: leave the result there (two-shot, in place)."""
+        assert not self.emulated, "use all_reduce_emulated for emulated groups"
+        _lib.check(self._lib.tfop_allreduce(
+            self._h, _lib.ptr(inp), _lib.dtype_tag(inp.dtype) if inp is not None else 0,
+            _lib.ptr(out), _lib.dtype_tag(out.dtype) if out is not None else 0,
+            _lib.dtype_tag(wire_dtype), n, sym_off, float(scale), algo, max_blocks,
+            _lib.stream_handle(stream)), "allreduce")
+
+    def check_error(self) -> bool:
+        flag = C.c_int(0)
+        _lib.check(self._lib.tfop_comm_check_error(self._h, C.byref(flag)), "comm_check_error")
+        return bool(flag.value)
+
+    def close(self):
+        if self._h:
+            self._views.clear()
+            self._lib.tfop_comm_destroy(self._h)
+            self._h = None
+
+
+def all_reduce_emulated(comms: Sequence[SymmetricComm], n: int, *,
+                        inps: Optional[Sequence[torch.Tensor]] = None,
+                        outs: Optional[Sequence[torch.Tensor]] = None, sym_off: int = 0,
+                        wire_dtype: torch.dtype = torch.bfloat16, scale: float = 1.0,
+                        algo: int = AUTO, max_blocks: int = 0, stream=None) -> None:
+    lib = _lib.load()
+    world = len(comms)
+    harr = (C.c_void_p * world)(*[c._h for c in comms])
+    iarr = (C.c_void_p * world)(*[t.data_ptr() for t in inps]) if inps is not None else None
+    oarr = (C.c_void_p * world)(*[t.data_ptr() for t in outs]) if outs is not None else None
+    _lib.check(lib.tfop_allreduce_emulated(
+        harr, world, iarr, _lib.dtype_tag(inps[0].dtype) if inps is not None else 0, oarr,
+        _lib.dtype_tag(outs[0].dtype) if outs is not None else 0, _lib.dtype_tag(wire_dtype), n,
+        sym_off, float(scale), algo, max_blocks, _lib.stream_handle(stream)),
+        "allreduce_emulated")
