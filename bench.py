@@ -104,10 +104,18 @@ def main():
     ap.add_argument("--no-fused-bn", action="store_true")
     ap.add_argument("--comm-blocks", type=int, default=32)
     ap.add_argument("--bucket-mb", type=int, default=16)
+    ap.add_argument("--stock-mode", default="autocast", choices=["autocast", "purebf16"],
+                    help="--impl stock: fp32 weights under torch.autocast(bf16) (the usual recipe) "
+                         "or a model cast to bf16")
     args = ap.parse_args()
     if args.impl == "reference":
         return _reference_arm()
     args.warmup = max(args.warmup, 3)
+
+    # Libraries (NCCL_DEBUG=VERSION, torchrun) may print to stdout; keep the real stdout
+    # for the single JSON line and send everything else to stderr.
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -189,7 +197,9 @@ def main():
         # "reference mode": stock torchvision-style graph, torch DDP over NCCL, torch SGD
         from tf_operator_b200.models.resnet import ResNet
         model = ResNet(args.depth, fused=False).to(dev).to(memory_format=torch.channels_last)
-        model = model.to(torch.bfloat16)
+        amp = args.stock_mode == "autocast"
+        if not amp:
+            model = model.to(torch.bfloat16)
         if world > 1:
             model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank],
                                                               gradient_as_bucket_view=True)
@@ -204,7 +214,8 @@ def main():
             x = ((xu8.permute(0, 3, 1, 2).float() - mean) / std).to(torch.bfloat16)
             x = x.contiguous(memory_format=torch.channels_last)
             opt.zero_grad(set_to_none=True)
-            loss = torch.nn.functional.cross_entropy(model(x).float(), y)
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                loss = torch.nn.functional.cross_entropy(model(x).float(), y)
             loss.backward()
             opt.step()
             return loss
@@ -270,7 +281,8 @@ def main():
                        "l2": "per-step working set (>10 GB of activations) far exceeds the "
                              "126 MB L2; host inputs rotate over 4 pinned batches",
                        "cuda_graph": args.impl == "native" and not args.no_graph,
-                       "fused_bn": args.impl == "native" and not args.no_fused_bn},
+                       "fused_bn": args.impl == "native" and not args.no_fused_bn,
+                       "stock_mode": args.stock_mode if args.impl == "stock" else None},
             "clocks": clocks,
             "e2e": {"value": round(gb / (e2e_ms / args.steps / 1e3), 2), "unit": "img/s",
                     "ms_per_step": round(e2e_ms / args.steps, 4),
@@ -278,7 +290,8 @@ def main():
                     "last_loss": round(last_loss, 4)},
             "gpu_launches": launches_per_step * args.steps,
         }
-        print(json.dumps(out))
+        real_stdout.write(json.dumps(out) + "\n")
+        real_stdout.flush()
     if world > 1:
         dist.destroy_process_group()
     return 0

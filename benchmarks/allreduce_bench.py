@@ -1,0 +1,129 @@
+#!/usr/bin/env python
+"""Multi-GPU check + microbenchmark of the fused P2P all-reduce against NCCL.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29511 benchmarks/allreduce_bench.py [--out gpurun_out/allreduce_N.json]
+
+Correctness: every rank's result must equal NCCL's sum within bf16 tolerance and be
+bitwise identical across ranks. Timing: CUDA events, max over ranks, L2 flushed
+between iterations is unnecessary here because peer data never sits in the local L2
+(peer loads bypass it) — stated in the output.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from tf_operator_b200.runtime.symm import ONE_SHOT, TWO_SHOT, SymmetricComm  # noqa: E402
+
+
+def timed(fn, iters, warm=5):
+    for _ in range(warm):
+        fn()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()) * 1e3  # us
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="")
+    ap.add_argument("--max-mb", type=int, default=256)
+    args = ap.parse_args()
+    rank = int(os.environ["RANK"])
+    world = int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    max_bytes = args.max_mb << 20
+    comm = SymmetricComm.from_torch_distributed(2 * max_bytes + (1 << 20))
+    results = {"world": world, "rows": [], "note": "CUDA events, max over ranks; peer loads bypass local L2"}
+    ok = True
+    sizes = [1 << 10, 8 << 10, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20, max_bytes]
+    # histogram shape of BASELINE config 5: 256 bins x 500 features x (g,h) fp32
+    hist_n = 256 * 500 * 2
+    for nbytes in sizes:
+        n = nbytes // 2
+        torch.manual_seed(100 + rank)
+        x = torch.randn(n, device=dev).bfloat16()
+        ref = x.clone().float()
+        dist.all_reduce(ref)
+        ref = ref / world
+        row = {"bytes": nbytes}
+        for name, algo in (("oneshot", ONE_SHOT), ("twoshot", TWO_SHOT)):
+            if algo == ONE_SHOT and nbytes > (8 << 20):
+                continue
+            out = torch.empty_like(x)
+            comm.all_reduce(n, inp=x, out=out, scale=1.0 / world, algo=algo)
+            torch.cuda.synchronize()
+            err = (out.float() - ref).abs().max().item()
+            gathered = [torch.empty_like(out) for _ in range(world)]
+            dist.all_gather(gathered, out)
+            same = all(torch.equal(g, gathered[0]) for g in gathered)
+            good = err < 0.05 and same and not comm.check_error()
+            ok &= good
+            us = timed(lambda: comm.all_reduce(n, inp=x, out=out, scale=1.0 / world, algo=algo), 20)
+            row[name] = {"us": round(us, 2), "max_err": err, "identical": same,
+                         "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
+        # in-place two-shot on symmetric memory (the DDP gradient-bucket mode)
+        sym = comm.view(0, n, torch.bfloat16)
+        sym.copy_(x)
+        dist.barrier()
+        torch.cuda.synchronize()
+        comm.all_reduce(n, sym_off=0, scale=1.0 / world, algo=TWO_SHOT)
+        torch.cuda.synchronize()
+        err = (sym.float() - ref).abs().max().item()
+        ok &= err < 0.05
+        us = timed(lambda: comm.all_reduce(n, sym_off=0, scale=1.0, algo=TWO_SHOT), 20)
+        row["twoshot_inplace"] = {"us": round(us, 2), "max_err": err,
+                                  "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
+        y = x.clone()
+        us = timed(lambda: dist.all_reduce(y), 20)
+        row["nccl"] = {"us": round(us, 2),
+                       "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
+        results["rows"].append(row)
+    # fp32 histogram all-reduce (K6)
+    h = torch.randn(hist_n, device=dev)
+    href = h.clone()
+    dist.all_reduce(href)
+    hout = torch.empty_like(h)
+    hrow = {"elements": hist_n, "bytes": hist_n * 4}
+    for name, algo in (("oneshot", ONE_SHOT), ("twoshot", TWO_SHOT)):
+        comm.all_reduce(hist_n, inp=h, out=hout, wire_dtype=torch.float32, algo=algo)
+        torch.cuda.synchronize()
+        err = (hout - href).abs().max().item()
+        ok &= err < 1e-3
+        us = timed(lambda: comm.all_reduce(hist_n, inp=h, out=hout, wire_dtype=torch.float32,
+                                           algo=algo), 50)
+        hrow[name] = {"us": round(us, 2), "max_err": err}
+    hy = h.clone()
+    hrow["nccl"] = {"us": round(timed(lambda: dist.all_reduce(hy), 50), 2)}
+    results["histogram_f32"] = hrow
+    results["ok"] = bool(ok)
+    if rank == 0:
+        print(json.dumps(results))
+        if args.out:
+            with open(args.out, "w") as f:
+                json.dump(results, f, indent=1)
+    dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,108 @@
+#!/usr/bin/env python
+"""Single-GPU kernel microbenchmarks with roofline fractions (of measured peaks).
+
+CUDA events on the launching stream, 5 warm-up + N timed iterations, an L2 flush
+(write of a 256 MB buffer) between timed iterations.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from tf_operator_b200.ops import optim as fo  # noqa: E402
+from tf_operator_b200.ops.bn import fused_bn_act  # noqa: E402
+from tf_operator_b200.ops.gemm import gemm_tn  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], "measured"
+    return 6650.0, 1590.0, "fallback"
+
+
+_flush = None
+
+
+def timed(fn, iters=10, warm=5):
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(warm):
+        fn()
+    tot = 0.0
+    for _ in range(iters):
+        _flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / iters * 1e3  # us
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    hbm, tf, src = peaks()
+    res = {"peaks": {"hbm_gbs": hbm, "bf16_tflops": tf, "source": src}, "gemm": [], "bn": [], "optim": []}
+    torch.manual_seed(0)
+    for (m, n, k) in [(8192, 8192, 8192), (4096, 4096, 4096), (16384, 4096, 1024), (16384, 1024, 4096),
+                      (8192, 1024, 1024), (4096, 1000, 2048)]:
+        a = torch.randn(m, k, device="cuda").bfloat16()
+        b = torch.randn(n, k, device="cuda").bfloat16()
+        row = {"m": m, "n": n, "k": k}
+        for tn in (128, 256):
+            us = timed(lambda: gemm_tn(a, b, tile_n=tn))
+            row[f"tcgen05_tile{tn}_tflops"] = round(2 * m * n * k / us / 1e6, 1)
+        us = timed(lambda: torch.matmul(a, b.t()))
+        row["cublas_tflops"] = round(2 * m * n * k / us / 1e6, 1)
+        best = max(row["tcgen05_tile128_tflops"], row["tcgen05_tile256_tflops"])
+        row["frac_of_peak"] = round(best / tf, 3)
+        row["vs_cublas"] = round(best / row["cublas_tflops"], 3)
+        res["gemm"].append(row)
+    for shape in [(256, 64, 112, 112), (256, 256, 56, 56), (256, 512, 28, 28), (256, 1024, 14, 14), (256, 2048, 7, 7)]:
+        n, c, h, w = shape
+        x = torch.randn(shape, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+        r = torch.randn(shape, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+        g = torch.ones(c, device="cuda").bfloat16().requires_grad_(True)
+        bt = torch.zeros(c, device="cuda").bfloat16().requires_grad_(True)
+        rm, rv = torch.zeros(c, device="cuda"), torch.ones(c, device="cuda")
+        nbytes = x.numel() * 2
+        us_f = timed(lambda: fused_bn_act(x, g, bt, rm, rv, True, 0.1, 1e-5, True, r))
+        y = fused_bn_act(x, g, bt, rm, rv, True, 0.1, 1e-5, True, r)
+        dy = torch.randn_like(y)
+        us_b = timed(lambda: torch.autograd.grad(y, (x, g, bt), dy, retain_graph=True))
+        # algorithmic bytes: fwd = x twice + res + y (+mask/16); bwd = 2*(dy + x) + dx + dres
+        fwd_b, bwd_b = nbytes * 4 + nbytes // 16, nbytes * 6 + nbytes // 8
+        xs = x.detach()
+        bn = torch.nn.BatchNorm2d(c).cuda().bfloat16()
+        us_stock = timed(lambda: torch.relu(bn(xs) + r))
+        res["bn"].append({"shape": list(shape), "fwd_us": round(us_f, 1), "bwd_us": round(us_b, 1),
+                          "fwd_GBps": round(fwd_b / us_f / 1e3, 1), "bwd_GBps": round(bwd_b / us_b / 1e3, 1),
+                          "fwd_frac_hbm": round(fwd_b / us_f / 1e3 / hbm, 3),
+                          "bwd_frac_hbm": round(bwd_b / us_b / 1e3 / hbm, 3),
+                          "stock_bn_add_relu_fwd_us": round(us_stock, 1)})
+    n = 25_600_000
+    master, mom = torch.randn(n, device="cuda"), torch.zeros(n, device="cuda")
+    grad = torch.randn(n, device="cuda").bfloat16()
+    w16 = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    hp = torch.tensor([0.1, 0.9, 1e-4, 1.0, 0.9, 0.999, 1e-8, 1.0], device="cuda")
+    us = timed(lambda: fo.sgd_momentum_(master, mom, grad, w16, n, hp))
+    by = n * (2 + 4 + 4 + 4 + 4 + 2)
+    res["optim"].append({"kernel": "sgd_momentum", "n": n, "us": round(us, 1),
+                         "GBps": round(by / us / 1e3, 1), "frac_hbm": round(by / us / 1e3 / hbm, 3)})
+    print(json.dumps(res))
+    if args.out:
+        json.dump(res, open(args.out, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
