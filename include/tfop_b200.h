@@ -107,6 +107,13 @@ int tfop_bn_bwd_apply(const void* dy, const void* x, const void* mask, const flo
                       const float* coef, void* dx, void* dres, size_t M, int C,
                       cudaStream_t stream);
 
+/* ---- MaxPool 3x3/2 pad 1, NHWC bf16 (csrc/pool.cu) -----------------------
+ * No reference counterpart; ResNet stem pool. idx: 1 byte per output element. */
+int tfop_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C,
+                          cudaStream_t stream);
+int tfop_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C,
+                          cudaStream_t stream);
+
 /* ---- K7: tcgen05 / TMEM / TMA bf16 GEMM (csrc/gemm_tcgen05.cu) -----------
  * C[M,N] = epi(A[M,K] * B[N,K]^T + bias); the dense layers of
  * examples/v1/dist-mnist/dist_mnist.py:188-192. epilogue: 0 none, 1 bias,

@@ -194,3 +194,23 @@ def test_allreduce_emulated_in_place_two_shot(dev):
     finally:
         for c in comms:
             c.close()
+
+
+# ----------------------------------------------------------------------------- max pool
+@pytest.mark.parametrize("shape", [(4, 64, 112, 112), (2, 8, 7, 9), (3, 128, 15, 14)])
+def test_maxpool_3x3_s2_matches_torch(dev, shape):
+    from tf_operator_b200.ops.pool import max_pool_3x3_s2
+    torch.manual_seed(5)
+    x = torch.randn(shape, device=dev).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = max_pool_3x3_s2(x)
+    xr = x.detach().float().requires_grad_(True)
+    yr = F.max_pool2d(xr, 3, 2, 1)
+    assert torch.equal(y.float(), yr)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    yr.backward(dy.float())
+    # ties (equal bf16 values in one window) may pick a different tap than torch's fp32 scan
+    # only when values are exactly equal, in which case the gradient mass is the same
+    torch.testing.assert_close(x.grad.float().sum(), xr.grad.sum(), rtol=1e-2, atol=1e-1)
+    mism = (x.grad.float() - xr.grad).abs() > 2e-2
+    assert mism.float().mean() < 1e-3

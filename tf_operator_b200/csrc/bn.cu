@@ -26,6 +26,7 @@ constexpr int kGroupC = 64;      // channels per block column
 constexpr int kMaxC = 4096;
 constexpr int kMaxGroups = kMaxC / kGroupC;
 constexpr int kTargetBlocks = 148 * 8;
+constexpr int kU = 4;            // rows in flight per thread (memory-level parallelism)
 
 __device__ __forceinline__ float ld_param(const void* p, int dtype, int i) {
     return dtype == TFOP_F32 ? ((const float*)p)[i]
@@ -77,7 +78,7 @@ __device__ __forceinline__ bool last_block_ticket(unsigned int* counter, int* s_
     return last;
 }
 
-__global__ void __launch_bounds__(kT) bn_fwd_stats_kernel(
+__global__ void __launch_bounds__(kT, 4) bn_fwd_stats_kernel(
     const __nv_bfloat16* __restrict__ x, size_t M, int C, float* __restrict__ accum,
     unsigned int* __restrict__ counters, const void* __restrict__ gamma,
     const void* __restrict__ beta, int param_dtype, float* __restrict__ running_mean,
@@ -92,14 +93,22 @@ __global__ void __launch_bounds__(kT) bn_fwd_stats_kernel(
 #pragma unroll
     for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
     const size_t rstride = (size_t)gridDim.x * 32;
-    for (size_t r = (size_t)blockIdx.x * 32 + ty; r < M; r += rstride) {
-        const uint4 raw = ld_stream_v4(xp + r * C);
-        float f[8];
-        bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&raw), f);
+    for (size_t r = (size_t)blockIdx.x * 32 + ty; r < M; r += rstride * kU) {
+        uint4 raw[kU];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            s[i] += f[i];
-            q[i] = fmaf(f[i], f[i], q[i]);
+        for (int u = 0; u < kU; ++u) {
+            const size_t rr = r + (size_t)u * rstride;
+            raw[u] = rr < M ? ld_nc_v4(xp + rr * C) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            float f[8];
+            bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&raw[u]), f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                s[i] += f[i];
+                q[i] = fmaf(f[i], f[i], q[i]);
+            }
         }
     }
     block_fold_atomic(s, q, C, c_base, accum, smem);
@@ -130,7 +139,7 @@ __global__ void __launch_bounds__(kT) bn_fwd_stats_kernel(
 }
 
 template <bool RELU, bool RES>
-__global__ void __launch_bounds__(kT) bn_fwd_apply_kernel(
+__global__ void __launch_bounds__(kT, 4) bn_fwd_apply_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
     __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ mask,
     const float* __restrict__ scale_shift, size_t M, int C) {
@@ -144,34 +153,47 @@ __global__ void __launch_bounds__(kT) bn_fwd_apply_kernel(
         b[i] = scale_shift[C + c0 + i];
     }
     const size_t rstride = (size_t)gridDim.x * 32;
-    for (size_t r = (size_t)blockIdx.x * 32 + ty; r < M; r += rstride) {
-        const size_t e = r * C + c0;
-        const uint4 raw = ld_stream_v4(x + e);
-        float f[8];
-        bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&raw), f);
-        if (RES) {
-            const uint4 rr = ld_stream_v4(res + e);
-            float rv[8];
-            bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&rr), rv);
+    constexpr int U = RES ? 2 : 4;
+    for (size_t r0 = (size_t)blockIdx.x * 32 + ty; r0 < M; r0 += rstride * U) {
+        uint4 raw[U], rres[U];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], a[i], b[i]) + rv[i];
-        } else {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], a[i], b[i]);
-        }
-        if (RELU) {
-            unsigned int m = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                if (f[i] > 0.f)
-                    m |= 1u << i;
-                else
-                    f[i] = 0.f;
+        for (int u = 0; u < U; ++u) {
+            const size_t r = r0 + (size_t)u * rstride;
+            if (r < M) {
+                raw[u] = ld_stream_v4(x + r * C + c0);
+                if (RES) rres[u] = ld_stream_v4(res + r * C + c0);
             }
-            if (mask) mask[r * CV + (c0 >> 3)] = (uint8_t)m;
         }
-        bf16x8 pk = f32_to_bf16x8(f);
-        *reinterpret_cast<uint4*>(y + e) = *reinterpret_cast<uint4*>(&pk);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t r = r0 + (size_t)u * rstride;
+            if (r >= M) break;
+            const size_t e = r * C + c0;
+            float f[8];
+            bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&raw[u]), f);
+            if (RES) {
+                float rv[8];
+                bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&rres[u]), rv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], a[i], b[i]) + rv[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], a[i], b[i]);
+            }
+            if (RELU) {
+                unsigned int m = 0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (f[i] > 0.f)
+                        m |= 1u << i;
+                    else
+                        f[i] = 0.f;
+                }
+                if (mask) mask[r * CV + (c0 >> 3)] = (uint8_t)m;
+            }
+            bf16x8 pk = f32_to_bf16x8(f);
+            *reinterpret_cast<uint4*>(y + e) = *reinterpret_cast<uint4*>(&pk);
+        }
     }
 }
 
@@ -200,8 +222,8 @@ __global__ void __launch_bounds__(kT) bn_bwd_reduce_kernel(
     const size_t rstride = (size_t)gridDim.x * 32;
     for (size_t r = (size_t)blockIdx.x * 32 + ty; r < M; r += rstride) {
         const size_t e = r * C + c0;
-        const uint4 rd = ld_stream_v4(dy + e);
-        const uint4 rx = ld_stream_v4(x + e);
+        const uint4 rd = ld_nc_v4(dy + e);
+        const uint4 rx = ld_nc_v4(x + e);
         float d[8], f[8];
         bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&rd), d);
         bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&rx), f);

@@ -65,12 +65,15 @@ __device__ __forceinline__ bf16x8 f32_to_bf16x8(const float* f) {
 // 16-byte global loads/stores. The *_peer variants are used on pointers that
 // may map a peer GPU over NVLink: they are plain coherent accesses (peer
 // memory bypasses the local L2, see B300_MICROARCH "NVLink").
-__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-    return r;
+// Read-only streaming loads. These are compiler intrinsics rather than asm
+// volatile so ptxas is free to hoist a batch of them ahead of their uses (an
+// asm volatile load was observed to be scheduled load-use-load-use, i.e. one
+// request in flight per thread).
+__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {   // evict-first: data read once
+    return __ldcs(reinterpret_cast<const uint4*>(p));
+}
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {       // default policy: re-read soon
+    return __ldg(reinterpret_cast<const uint4*>(p));
 }
 __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
     uint4 r;
@@ -86,9 +89,7 @@ __device__ __forceinline__ void st_peer_v4(void* p, const uint4& v) {
                  : "memory");
 }
 __device__ __forceinline__ void st_stream_v4(void* p, const uint4& v) {
-    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
-                 "r"(v.y), "r"(v.z), "r"(v.w)
-                 : "memory");
+    __stcs(reinterpret_cast<uint4*>(p), v);
 }
 
 // system-scope flag signalling (K8 primitives)

@@ -13,6 +13,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from ..ops.bn import FusedBatchNorm2d
+from ..ops.pool import MaxPool3x3s2
 
 
 class _StockBNAct(nn.Module):
@@ -92,7 +93,7 @@ class ResNet(nn.Module):
         block, layers = _CFG[depth]
         self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
         self.bn1 = _bn(width, True, fused)
-        self.pool = nn.MaxPool2d(3, stride=2, padding=1)
+        self.pool = MaxPool3x3s2() if fused else nn.MaxPool2d(3, stride=2, padding=1)
         stages, cin = [], width
         for i, nblk in enumerate(layers):
             w = width * (2 ** i)
