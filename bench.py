@@ -102,6 +102,8 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--no-fused-bn", action="store_true")
+    ap.add_argument("--no-s2d-stem", action="store_true",
+                    help="feed the stem conv plain NHWC x3 input instead of the space-to-depth layout")
     ap.add_argument("--comm-blocks", type=int, default=32)
     ap.add_argument("--bucket-mb", type=int, default=16)
     ap.add_argument("--stock-mode", default="autocast", choices=["autocast", "purebf16"],
@@ -168,7 +170,8 @@ def main():
         eng = DataParallelEngine(model, comm=comm, batch_size=B, image_size=S, lr=0.1,
                                  momentum=0.9, weight_decay=1e-4, graph=not args.no_graph,
                                  overlap=not args.no_overlap, comm_blocks=args.comm_blocks,
-                                 bucket_bytes=args.bucket_mb << 20)
+                                 bucket_bytes=args.bucket_mb << 20,
+                                 stem_s2d=not args.no_s2d_stem)
 
         def device_step():
             eng.run_device_step()
@@ -282,6 +285,8 @@ def main():
                              "126 MB L2; host inputs rotate over 4 pinned batches",
                        "cuda_graph": args.impl == "native" and not args.no_graph,
                        "fused_bn": args.impl == "native" and not args.no_fused_bn,
+                       "stem": "space-to-depth 4x4 conv (same 7x7 parameters)"
+                               if args.impl == "native" and not args.no_s2d_stem else "7x7/2",
                        "stock_mode": args.stock_mode if args.impl == "stock" else None},
             "clocks": clocks,
             "e2e": {"value": round(gb / (e2e_ms / args.steps / 1e3), 2), "unit": "img/s",

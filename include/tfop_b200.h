@@ -87,6 +87,11 @@ int tfop_multi_pack_bf16(const tfop_pack_seg* segs, int nseg, int src_dtype, voi
 int tfop_u8_to_bf16_normalize(const void* in_u8, void* out_bf16, size_t n, int channels,
                               const float* mean, const float* stdv, cudaStream_t stream);
 
+/* uint8 [N,H,W,3] -> bf16 [N,H/2+3,W/2+3,16]: space-to-depth layout under which the
+ * ResNet 7x7/2 stem conv is a 4x4/1 conv over 16 channels (no reference counterpart). */
+int tfop_stem_space_to_depth(const void* in_u8, void* out_bf16, int N, int H, int W,
+                             const float* mean, const float* stdv, cudaStream_t stream);
+
 /* ---- fused BatchNorm / ReLU / residual, NHWC bf16 (csrc/bn.cu) -----------
  * No reference counterpart (the reference ships no kernels); compute side of
  * the PyTorchJob ResNet-50 config. `workspace` = tfop_bn_workspace_bytes()

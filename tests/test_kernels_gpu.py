@@ -214,3 +214,21 @@ def test_maxpool_3x3_s2_matches_torch(dev, shape):
     torch.testing.assert_close(x.grad.float().sum(), xr.grad.sum(), rtol=1e-2, atol=1e-1)
     mism = (x.grad.float() - xr.grad).abs() > 2e-2
     assert mism.float().mean() < 1e-3
+
+
+def test_stem_space_to_depth_matches_7x7_conv(dev):
+    from tf_operator_b200.ops.preproc import (IMAGENET_MEAN, IMAGENET_STD, stem_space_to_depth,
+                                              stem_weight_s2d)
+    torch.manual_seed(6)
+    x = torch.randint(0, 256, (3, 64, 48, 3), dtype=torch.uint8, device=dev)
+    w = torch.randn(16, 3, 7, 7, device=dev)
+    m = torch.tensor(IMAGENET_MEAN, device=dev)
+    s = torch.tensor(IMAGENET_STD, device=dev)
+    xn = ((x.float() / 255 - m) / s).permute(0, 3, 1, 2)
+    ref = F.conv2d(xn, w, stride=2, padding=3)
+    xs = stem_space_to_depth(x)
+    assert xs.shape == (3, 16, 35, 27)
+    cpu = stem_space_to_depth(x.cpu())
+    torch.testing.assert_close(xs.float().cpu(), cpu.float(), rtol=0, atol=0)
+    out = F.conv2d(xs.float(), stem_weight_s2d(w).float())
+    torch.testing.assert_close(out, ref, rtol=2e-2, atol=0.3)

@@ -69,3 +69,73 @@ TFOP_API int tfop_u8_to_bf16_normalize(const void* in_u8, void* out_bf16, size_t
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Stem space-to-depth: uint8 [N,H,W,3] -> bf16 [N, H/2+3, W/2+3, 16], normalised.
+// A 7x7 / stride-2 / pad-3 convolution over 3 channels equals a 4x4 / stride-1 / pad-0
+// convolution over this tensor (2x2 pixel blocks folded into 12 channels, padded to 16;
+// two zero block-rows/cols in front and one behind supply the padding), which lets the
+// library pick tensor-core kernels instead of the 3-channel special case.
+// out[n, j+2, l+2, (bh*2+bw)*3 + ch] = norm(in[n, 2j+bh, 2l+bw, ch])
+// ---------------------------------------------------------------------------
+namespace {
+
+__global__ void __launch_bounds__(256) stem_s2d_kernel(const uint8_t* __restrict__ in,
+                                                       __nv_bfloat16* __restrict__ out, int N,
+                                                       int H, int W, Norm nm) {
+    const int Hb = H / 2, Wb = W / 2;       // blocks
+    const int Ho = Hb + 3, Wo = Wb + 3;     // padded block grid
+    const unsigned int total = (unsigned int)N * Ho * Wo;
+    const unsigned int stride = gridDim.x * blockDim.x;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int l = (int)(t % Wo) - 2;
+        unsigned int p = t / Wo;
+        const int j = (int)(p % Ho) - 2;
+        const int n = (int)(p / Ho);
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = 0.f;
+        if (j >= 0 && j < Hb && l >= 0 && l < Wb) {
+#pragma unroll
+            for (int bh = 0; bh < 2; ++bh) {
+                // the two horizontally adjacent pixels are 6 consecutive bytes
+                const uint8_t* src = in + (((size_t)n * H + (2 * j + bh)) * W + 2 * l) * 3;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) {
+                    const int ch = k % 3;
+                    f[bh * 6 + k] = (float)src[k] * nm.scale[ch] + nm.bias[ch];
+                }
+            }
+        }
+        bf16x8 lo = f32_to_bf16x8(f);
+        bf16x8 hi = f32_to_bf16x8(f + 8);
+        uint4* dst = reinterpret_cast<uint4*>(out + (size_t)t * 16);
+        dst[0] = *reinterpret_cast<uint4*>(&lo);
+        dst[1] = *reinterpret_cast<uint4*>(&hi);
+    }
+}
+
+}  // namespace
+
+// in: uint8 [N,H,W,3] (H, W even); out: bf16 [N, H/2+3, W/2+3, 16].
+TFOP_API int tfop_stem_space_to_depth(const void* in_u8, void* out_bf16, int N, int H, int W,
+                                      const float* mean, const float* stdv,
+                                      cudaStream_t stream) {
+    TFOP_REQUIRE(N > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "H and W must be even");
+    TFOP_REQUIRE((((uintptr_t)out_bf16) & 15) == 0, "output must be 16-byte aligned");
+    Norm nm;
+    for (int c = 0; c < 4; ++c) {
+        const float s = c < 3 ? stdv[c] : 1.f;
+        const float m = c < 3 ? mean[c] : 0.f;
+        nm.scale[c] = 1.f / (255.f * s);
+        nm.bias[c] = -m / s;
+    }
+    const size_t total = (size_t)N * (H / 2 + 3) * (W / 2 + 3);
+    TFOP_REQUIRE(total < 0xffffffffull, "tensor too large for 32-bit indexing");
+    size_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    stem_s2d_kernel<<<(int)blocks, 256, 0, stream>>>((const uint8_t*)in_u8,
+                                                     (__nv_bfloat16*)out_bf16, N, H, W, nm);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}

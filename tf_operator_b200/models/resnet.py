@@ -14,6 +14,7 @@ import torch.nn.functional as F
 
 from ..ops.bn import FusedBatchNorm2d
 from ..ops.pool import MaxPool3x3s2
+from ..ops.preproc import stem_weight_s2d
 
 
 class _StockBNAct(nn.Module):
@@ -108,7 +109,13 @@ class ResNet(nn.Module):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
 
     def forward(self, x):
-        x = self.pool(self.bn1(self.conv1(x)))
+        if x.shape[1] == 16:
+            # input already in the stem's space-to-depth layout (ops/preproc.py): the 7x7/2
+            # convolution runs as a 4x4/1 convolution over 16 channels, same parameters
+            x = F.conv2d(x, stem_weight_s2d(self.conv1.weight))
+        else:
+            x = self.conv1(x)
+        x = self.pool(self.bn1(x))
         x = self.blocks(x)
         x = F.adaptive_avg_pool2d(x, 1).flatten(1)
         return self.fc(x)

@@ -45,6 +45,8 @@ _SIGS = {
     "tfop_multi_pack_bf16": (c_int, [c_void_p, c_int, c_int, c_void_p, c_float, c_void_p]),
     "tfop_u8_to_bf16_normalize": (c_int, [c_void_p, c_void_p, c_size_t, c_int,
                                           C.POINTER(c_float), C.POINTER(c_float), c_void_p]),
+    "tfop_stem_space_to_depth": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int,
+                                         C.POINTER(c_float), C.POINTER(c_float), c_void_p]),
     "tfop_bn_workspace_bytes": (c_size_t, []),
     "tfop_bn_fwd_stats": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p, c_int, c_void_p,
                                   c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p,

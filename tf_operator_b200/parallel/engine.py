@@ -49,7 +49,7 @@ class DataParallelEngine:
                  nesterov: bool = False, bucket_bytes: int = 16 << 20, graph: bool = True,
                  overlap: bool = True, comm_blocks: int = 32,
                  loss_fn: Optional[Callable] = None, device: Optional[torch.device] = None,
-                 label_smoothing: float = 0.0):
+                 label_smoothing: float = 0.0, stem_s2d: bool = False):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.comm = comm
         self.world = comm.world if comm is not None else 1
@@ -78,7 +78,9 @@ class DataParallelEngine:
         # static device inputs / outputs (graph-friendly) + double-buffered staging
         shp = (batch_size, image_size, image_size, channels)
         self.x_u8 = torch.zeros(shp, dtype=torch.uint8, device=self.device)
-        self.x_bf16 = torch.zeros(shp, dtype=torch.bfloat16, device=self.device)
+        self.stem_s2d = stem_s2d and channels == 3 and image_size % 2 == 0
+        xshp = (batch_size, image_size // 2 + 3, image_size // 2 + 3, 16) if self.stem_s2d else shp
+        self.x_bf16 = torch.zeros(xshp, dtype=torch.bfloat16, device=self.device)
         self.labels = torch.zeros(batch_size, dtype=torch.int64, device=self.device)
         self.loss_dev = torch.zeros((), dtype=torch.float32, device=self.device)
         self._stage_x = [torch.zeros_like(self.x_u8) for _ in range(2)]
@@ -137,7 +139,10 @@ class DataParallelEngine:
         """fwd + bwd + gradient exchange + optimizer on the current stream."""
         from ..ops import _lib
         l0 = _lib.launches_total()
-        x = preproc.u8_to_bf16_normalize(self.x_u8, self.x_bf16)
+        if self.stem_s2d:
+            x = preproc.stem_space_to_depth(self.x_u8, self.x_bf16)
+        else:
+            x = preproc.u8_to_bf16_normalize(self.x_u8, self.x_bf16)
         for p in self.model.parameters():
             p.grad = None
         for b in self.flat.buckets:
