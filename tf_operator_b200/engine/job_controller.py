@@ -203,7 +203,7 @@ class JobController:
             if len(pod_slice) > 1:
                 log.warning("We have too many pods for %s %d", rt, index)
             elif len(pod_slice) == 0:
-                log.info("Need to create new pod: %s-%d", rt, index)
+                log.debug("Need to create new pod: %s-%d", rt, index)
                 master = self.is_master_role(replicas, rtype, index)
                 self.create_new_pod(job, rt, str(index), spec, master, replicas)
             else:
