@@ -1,0 +1,290 @@
+"""End-to-end control-plane suites against the single-box cluster (API server + operator +
+launcher), driven through the SDK and the fault-injecting test-server.
+
+Python re-expression of the reference's Argo/EKS e2e suites:
+simple_tfjob_tests.py, shutdown_policy_tests.py, cleanpod_policy_tests.py,
+replica_restart_policy_tests.py, estimator_runconfig_tests.py, pod_names_validation_tests.py,
+invalid_tfjob_tests.py — replicas are the same kind of fake workload (examples/test_server).
+"""
+import json
+import os
+import sys
+import time
+import urllib.request
+
+import pytest
+import yaml
+
+from tf_operator_b200.api import common as c
+from tf_operator_b200.cluster import LocalCluster
+from tf_operator_b200.launcher import netmap
+from tf_operator_b200.launcher.kubelet import KubeletOptions
+from tf_operator_b200.launcher.topology import synthetic
+from tf_operator_b200.sdk import PyTorchJobClient, TFJobClient
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TEST_APP = ["python", os.path.join(REPO, "examples", "test_server", "test_app.py")]
+
+
+@pytest.fixture()
+def cluster():
+    cl = LocalCluster(topology=synthetic(0), serve_http=True,
+                      kubelet_options=KubeletOptions(cwd=REPO, restart_backoff=0.05))
+    yield cl
+    cl.stop()
+
+
+def tfjob(name, replicas, policy="Never", clean=None, extra=None):
+    specs = {rt: {"replicas": n, "restartPolicy": policy, "template": {"spec": {"containers": [
+        {"name": "tensorflow", "image": "test-server:local", "command": TEST_APP}]}}}
+        for rt, n in replicas.items()}
+    job = {"apiVersion": "kubeflow.org/v1", "kind": "TFJob", "metadata": {"name": name, "namespace": "default"},
+           "spec": {"tfReplicaSpecs": specs}}
+    if clean:
+        job["spec"]["runPolicy"] = {"cleanPodPolicy": clean}
+    if extra:
+        job["spec"].update(extra)
+    return job
+
+
+def wait(pred, timeout=30.0, interval=0.02):
+    end = time.time() + timeout
+    while time.time() < end:
+        v = pred()
+        if v:
+            return v
+        time.sleep(interval)
+    raise AssertionError("timed out waiting for condition")
+
+
+def http_get(cluster, replica, path, port=2222, retries=200):
+    """Through the API server's service proxy, like the reference harness (util.py:108-139)."""
+    url = f"{cluster.api.url}/api/v1/namespaces/default/services/{replica}:{port}/proxy/{path}"
+    last = None
+    for _ in range(retries):
+        try:
+            with urllib.request.urlopen(url, timeout=5) as r:
+                return r.read().decode()
+        except Exception as e:  # noqa: BLE001 - server not listening yet
+            last = e
+            time.sleep(0.05)
+    raise AssertionError(f"GET {url} failed: {last}")
+
+
+def wait_running(cluster, name, n):
+    def ok():
+        pods = cluster.store.list("pods", "default", f"job-name={name}")
+        return len(pods) == n and all(p["status"]["phase"] == "Running" for p in pods)
+    wait(ok)
+    for p in cluster.store.list("pods", "default", f"job-name={name}"):
+        http_get(cluster, c.name_of(p), "")     # the replica's server is accepting connections
+
+
+def phases(cluster, name):
+    return {c.name_of(p): p["status"]["phase"] for p in cluster.store.list("pods", "default", f"job-name={name}")}
+
+
+# simple_tfjob_tests.py:26-90 — run, succeed, delete, re-create under the same name --------------
+def test_simple_job_two_trials(cluster):
+    cli = TFJobClient(cluster=cluster)
+    for trial in range(2):
+        cli.create(tfjob("simple", {"Chief": 1, "PS": 1, "Worker": 2}))
+        wait_running(cluster, "simple", 4)
+        assert cli.is_job_running("simple")
+        http_get(cluster, "simple-chief-0", "exit?exitCode=0")
+        cli.wait_for_job("simple", polling_interval=0.05, timeout_seconds=30)
+        assert cli.is_job_succeeded("simple")
+        cli.delete("simple")
+        wait(lambda: not cluster.store.list("pods", "default", "job-name=simple"))
+        assert cluster.store.list("services", "default", "job-name=simple") == []
+    evs = [e["message"] for e in cluster.store.list("events", "default")]
+    assert sum("Created pod: simple-" in m for m in evs) == 8
+    assert sum("Created service: simple-" in m for m in evs) == 8
+
+
+# pod_names_validation_tests.py:14,47-84 ----------------------------------------------------------
+def test_pod_and_service_names(cluster):
+    cli = TFJobClient(cluster=cluster)
+    cli.create(tfjob("names", {"Chief": 1, "PS": 2, "Worker": 3}))
+    wait_running(cluster, "names", 6)
+    expected = {"names-chief-0", "names-ps-0", "names-ps-1", "names-worker-0", "names-worker-1", "names-worker-2"}
+    assert cli.get_pod_names("names") == expected
+    assert {c.name_of(s) for s in cluster.store.list("services", "default")} == expected
+    assert cli.get_pod_names("names", master=True) == {"names-chief-0"}
+    assert cli.get_pod_names("names", replica_type="ps", replica_index=1) == {"names-ps-1"}
+
+
+# shutdown_policy_tests.py:25-93 ------------------------------------------------------------------
+@pytest.mark.parametrize("replicas,kill", [({"Chief": 1, "PS": 1, "Worker": 2}, "chief-0"),
+                                           ({"PS": 1, "Worker": 2}, "worker-0")])
+def test_shutdown_policy(cluster, replicas, kill):
+    cli = TFJobClient(cluster=cluster)
+    cli.create(tfjob("shut", replicas))
+    wait_running(cluster, "shut", sum(replicas.values()))
+    http_get(cluster, f"shut-{kill}", "exit?exitCode=0")
+    cli.wait_for_job("shut", polling_interval=0.05, timeout_seconds=30)
+    assert cli.is_job_succeeded("shut")
+
+
+# cleanpod_policy_tests.py:26-115 ----------------------------------------------------------------
+@pytest.mark.parametrize("policy,remaining", [
+    ("All", set()), ("Running", {"clean-chief-0"}), ("None", {"clean-chief-0", "clean-ps-0", "clean-worker-0"})])
+def test_clean_pod_policy(cluster, policy, remaining):
+    cli = TFJobClient(cluster=cluster)
+    cli.create(tfjob("clean", {"Chief": 1, "PS": 1, "Worker": 1}, clean=policy))
+    wait_running(cluster, "clean", 3)
+    http_get(cluster, "clean-chief-0", "exit?exitCode=0")
+    cli.wait_for_job("clean", polling_interval=0.05, timeout_seconds=30)
+    wait(lambda: set(phases(cluster, "clean")) == remaining)
+    time.sleep(0.2)
+    assert set(phases(cluster, "clean")) == remaining
+
+
+# replica_restart_policy_tests.py:27-156 -----------------------------------------------------------
+def _start_time(cluster, pod):
+    st = cluster.store.get("pods", "default", pod)["status"]["containerStatuses"][0]
+    return st["restartCount"], st["state"]
+
+
+@pytest.mark.parametrize("policy,code,restarts,final", [
+    ("Always", 0, True, None), ("Always", 1, True, None),
+    ("OnFailure", 1, True, None), ("OnFailure", 0, False, "Succeeded"),
+    ("Never", 1, False, "Failed"), ("Never", 0, False, "Succeeded"),
+    ("ExitCode", 1, False, "Failed"), ("ExitCode", 130, True, None),
+])
+def test_replica_restart_policy(cluster, policy, code, restarts, final):
+    cli = TFJobClient(cluster=cluster)
+    cli.create(tfjob("rp", {"Worker": 1, "PS": 1}, policy=policy))
+    wait_running(cluster, "rp", 2)
+    uid0 = cluster.store.get("pods", "default", "rp-worker-0")["metadata"]["uid"]
+    assert cluster.store.get("pods", "default", "rp-worker-0")["spec"]["restartPolicy"] == \
+        ("Never" if policy == "ExitCode" else policy)
+    http_get(cluster, "rp-worker-0", f"exit?exitCode={code}")
+    if restarts:
+        if policy == "ExitCode":
+            # the operator deletes the failed pod and re-creates the same name/index
+            wait(lambda: cluster.store.list("pods", "default", "job-name=rp,replica-type=worker") and
+                 cluster.store.get("pods", "default", "rp-worker-0")["metadata"]["uid"] != uid0)
+            job = cli.get("rp")
+            assert not c.is_failed(job["status"])
+        else:
+            # kubelet-style in-place restart: same pod object, restartCount grows
+            wait(lambda: cluster.store.get("pods", "default", "rp-worker-0")["status"]
+                 ["containerStatuses"][0]["restartCount"] >= 1)
+            assert cluster.store.get("pods", "default", "rp-worker-0")["metadata"]["uid"] == uid0
+        wait_running(cluster, "rp", 2)
+        assert cli.get_job_status("rp") in ("Running", "Restarting")
+    else:
+        cli.wait_for_job("rp", polling_interval=0.05, timeout_seconds=30)
+        assert cli.get_job_status("rp") == final
+
+
+# estimator_runconfig_tests.py:25-101 ----------------------------------------------------------------
+def test_estimator_runconfig(cluster):
+    cli = TFJobClient(cluster=cluster)
+    cli.create(tfjob("rc", {"Chief": 1, "PS": 2, "Worker": 2, "Evaluator": 1}))
+    wait_running(cluster, "rc", 6)
+    tfc = json.loads(http_get(cluster, "rc-worker-1", "tfconfig"))
+    assert tfc["task"] == {"type": "worker", "index": 1} and tfc["environment"] == "cloud"
+    assert tfc["cluster"]["ps"] == ["rc-ps-0.default.svc:2222", "rc-ps-1.default.svc:2222"]
+    for replica, ttype, tid, chief in (("rc-chief-0", "chief", 0, True), ("rc-worker-0", "worker", 0, False),
+                                       ("rc-worker-1", "worker", 1, False), ("rc-ps-1", "ps", 1, False)):
+        rc = json.loads(http_get(cluster, replica, "runconfig"))
+        assert rc["task_type"] == ttype and rc["task_id"] == tid and rc["is_chief"] is chief
+        assert rc["master"] == f"grpc://{replica}.default.svc:2222"
+        assert rc["num_worker_replicas"] == 3 and rc["num_ps_replicas"] == 2
+        assert set(rc["cluster_spec"]) == {"chief", "ps", "worker"}
+    ev = json.loads(http_get(cluster, "rc-evaluator-0", "runconfig"))
+    assert ev["cluster_spec"] == {} and ev["task_type"] == "evaluator" and ev["master"] == ""
+    assert ev["num_worker_replicas"] == 0 and ev["num_ps_replicas"] == 0
+
+
+# invalid_tfjob_tests.py:26-44 -------------------------------------------------------------------------
+def test_invalid_tfjob_is_rejected_by_the_api_server(cluster):
+    cli = TFJobClient(cluster=cluster)
+    with pytest.raises(RuntimeError) as e:
+        cli.create({"apiVersion": "kubeflow.org/v1", "kind": "TFJob", "metadata": {"name": "invalid"},
+                    "spec": {"notTheActualField": {}}})
+    assert "spec.tfReplicaSpecs: Required value" in str(e.value)
+
+
+def test_legacy_invalid_spec_marks_job_failed():
+    """Legacy tf-operator.v1 behaviour (job.go:62-112): a spec that fails validation gets a
+    Failed condition with reason InvalidTFJobSpec written to /status."""
+    from tf_operator_b200.operator.manager import ManagerOptions
+    cl = LocalCluster(topology=synthetic(0), manager_options=ManagerOptions(
+        enabled_schemes=["TFJob"], fail_invalid_spec=True))
+    try:
+        bad = tfjob("bad", {"Worker": 1})
+        bad["spec"]["tfReplicaSpecs"]["Worker"]["template"]["spec"]["containers"][0]["name"] = "main"
+        cl.store.create("tfjobs", bad)
+        def failed():
+            st = cl.store.get("tfjobs", "default", "bad").get("status") or {}
+            cd = c.get_condition(st, "Failed") if st.get("conditions") else None
+            return cd
+        cd = wait(failed)
+        assert cd["reason"] == "InvalidTFJobSpec"
+        assert cl.store.list("pods") == []
+    finally:
+        cl.stop()
+
+
+# gang admission (pod.go:220-237 + Volcano semantics) -----------------------------------------------
+def test_gang_admission_is_all_or_nothing():
+    from tf_operator_b200.operator.manager import ManagerOptions
+    cl = LocalCluster(topology=synthetic(2), serve_http=True,
+                      manager_options=ManagerOptions(enable_gang_scheduling=True),
+                      kubelet_options=KubeletOptions(cwd=REPO, gpus_per_replica_default=1))
+    try:
+        cli = TFJobClient(cluster=cl)
+        cli.create(tfjob("big", {"Worker": 3}))         # wants 3 GPUs, box has 2
+        time.sleep(0.5)
+        assert set(phases(cl, "big").values()) == {"Pending"}
+        assert cl.kubelet.free_gpus() == [0, 1]          # nothing was claimed partially
+        assert cl.store.get("podgroups", "default", "big")["spec"]["minMember"] == 3
+        cli.create(tfjob("fits", {"Worker": 2}))
+        wait_running(cl, "fits", 2)
+        assert cl.kubelet.free_gpus() == []
+        envs = [json.loads(http_get(cl, f"fits-worker-{i}", "env")) for i in range(2)]
+        assert sorted(e["CUDA_VISIBLE_DEVICES"] for e in envs) == ["0", "1"]
+        assert set(phases(cl, "big").values()) == {"Pending"}
+    finally:
+        cl.stop()
+
+
+# BASELINE.json config 1 ---------------------------------------------------------------------------------
+def test_dist_mnist_tfjob_1ps_2workers_cpu(cluster):
+    job = yaml.safe_load(open(os.path.join(REPO, "examples", "dist_mnist", "tf_job_mnist.yaml")))
+    for spec in job["spec"]["tfReplicaSpecs"].values():
+        cmd = spec["template"]["spec"]["containers"][0]["command"]
+        spec["template"]["spec"]["containers"][0]["command"] = [
+            a.replace("--train_steps=200", "--train_steps=60") for a in cmd]
+    cli = TFJobClient(cluster=cluster)
+    cli.create(job)
+    done = cli.wait_for_job("dist-mnist-for-e2e-test", polling_interval=0.2, timeout_seconds=120)
+    assert cli.is_job_succeeded("dist-mnist-for-e2e-test"), done["status"]
+    logs = cli.get_logs("dist-mnist-for-e2e-test", master=True)
+    text = logs["dist-mnist-for-e2e-test-worker-0"]
+    assert "validation cross entropy" in text and "job name = worker" in text
+    # PS never exits by itself; cleanPodPolicy=Running (the TFJob default) removed it
+    wait(lambda: "dist-mnist-for-e2e-test-ps-0" not in phases(cluster, "dist-mnist-for-e2e-test"))
+
+
+def test_pytorchjob_env_rendezvous_gloo(cluster):
+    """PyTorchJob: MASTER_ADDR/RANK/WORLD_SIZE contract drives a real gloo all-reduce."""
+    script = ("import torch, torch.distributed as dist;"
+              "from tf_operator_b200.runtime.env import ReplicaContext;"
+              "ctx = ReplicaContext.from_env(); ctx.init_process_group('gloo');"
+              "t = torch.ones(4) * (ctx.rank + 1); dist.all_reduce(t);"
+              "print('rank', ctx.rank, 'world', ctx.world_size, 'sum', t[0].item())")
+    spec = lambda n: {"replicas": n, "restartPolicy": "Never", "template": {"spec": {"containers": [  # noqa: E731
+        {"name": "pytorch", "image": "x", "command": ["python", "-c", script]}]}}}
+    job = {"apiVersion": "kubeflow.org/v1", "kind": "PyTorchJob", "metadata": {"name": "ptg", "namespace": "default"},
+           "spec": {"pytorchReplicaSpecs": {"Master": spec(1), "Worker": spec(2)}}}
+    cli = PyTorchJobClient(cluster=cluster)
+    cli.create(job)
+    cli.wait_for_job("ptg", polling_interval=0.2, timeout_seconds=120)
+    assert cli.is_job_succeeded("ptg")
+    logs = cli.get_logs("ptg", master=False)
+    assert "rank 0 world 3 sum 6.0" in logs["ptg-master-0"]
+    assert "rank 2 world 3 sum 6.0" in logs["ptg-worker-1"]
