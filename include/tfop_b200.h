@@ -102,6 +102,18 @@ int tfop_bn_fwd_stats(const void* x, size_t M, int C, const void* gamma, const v
                       int param_dtype, float* running_mean, float* running_var, float momentum,
                       float eps, float* scale_shift, float* save_mean, float* save_invstd,
                       void* workspace, cudaStream_t stream);
+/* Allocation-free variant of tfop_bn_fwd_stats. It has no counterpart in the reference.
+ * For callers that must not allocate device memory (the GPU is owned by the host
+ * application's pool allocator, or cudaMalloc's device synchronisation is unacceptable):
+ * the scratch is a built-in 33,024-byte __device__ array, so C <= 4096 channels (larger C is
+ * an error). One array per device, shared by every call and cleared at the start of each:
+ * calls that overlap on the GPU race, keep them on one stream. The first call on a device
+ * resolves the array's address; make it before any stream capture. */
+int tfop_bn_fwd_stats_noalloc(const void* x, size_t M, int C, const void* gamma,
+                              const void* beta, int param_dtype, float* running_mean,
+                              float* running_var, float momentum, float eps,
+                              float* scale_shift, float* save_mean, float* save_invstd,
+                              cudaStream_t stream);
 int tfop_bn_fwd_apply(const void* x, const void* res, void* y, void* mask,
                       const float* scale_shift, size_t M, int C, int relu, cudaStream_t stream);
 int tfop_bn_bwd_reduce(const void* dy, const void* x, const void* mask, const float* save_mean,

@@ -413,3 +413,81 @@ TFOP_API int tfop_bn_bwd_apply(const void* dy, const void* x, const void* mask,
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of tfop_bn_fwd_stats.
+//
+// Who needs it: a caller that must not allocate device memory when it runs BatchNorm
+// statistics. Two cases we have met: (a) a host application that reserves the whole GPU
+// for its own pool allocator at start-up, so a later cudaMalloc from a plug-in either
+// fails or eats into memory the pool believes it owns; (b) a latency-critical loop where
+// cudaMalloc / cudaFree are off limits because they synchronise the device. Such a caller
+// cannot create the workspace tfop_bn_fwd_stats() asks for, so this entry point brings
+// its own: the cross-block accumulators and ticket counters live in the file-scope
+// __device__ array below, which every GPU that loads this library carries until exit.
+//
+// Limit: kNoAllocMaxC = 4096 channels (2*4096 floats + 64 counters = 33,024 bytes). A
+// larger C is rejected with an error; nothing is truncated.
+//
+// Sharing: there is ONE scratch array per device and every call uses it, keeping whatever
+// the previous call left. The accumulators and counters must start at zero, so each call
+// clears them on `stream` before the kernel. Two calls that overlap on the GPU (different
+// streams, or different host threads on different streams) race on the array: serialise
+// them on one stream.
+//
+// Set-up: in host code the array's name is only a host-side stand-in, not a device
+// address, so the first call on each device looks the real address up with
+// cudaGetSymbolAddress (that device being current) and caches it. Make that first call
+// before starting any stream capture.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr int kNoAllocMaxC = kMaxC;
+constexpr size_t kNoAllocScratchBytes =
+    (size_t)2 * kNoAllocMaxC * sizeof(float) + kMaxGroups * sizeof(unsigned int);
+
+static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+void* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// Device address of the scratch array on the current device (looked up once per device).
+int noalloc_scratch(void** out) {
+    int dev = -1;
+    TFOP_CUDA(cudaGetDevice(&dev));
+    TFOP_REQUIRE(dev >= 0 && dev < kMaxDevices, "device index out of range for the scratch table");
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        TFOP_CUDA(cudaGetSymbolAddress(&p, g_bn_noalloc_scratch));
+        TFOP_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+// Same contract and outputs as tfop_bn_fwd_stats, minus the workspace argument; performs
+// no cudaMalloc / cudaFree and calls no allocating library routine. C must be a multiple
+// of 64 and at most 4096. See the block comment above for sharing and first-call rules.
+TFOP_API int tfop_bn_fwd_stats_noalloc(const void* x, size_t M, int C, const void* gamma,
+                                       const void* beta, int param_dtype, float* running_mean,
+                                       float* running_var, float momentum, float eps,
+                                       float* scale_shift, float* save_mean, float* save_invstd,
+                                       cudaStream_t stream) {
+    TFOP_REQUIRE(C <= kNoAllocMaxC,
+                 "tfop_bn_fwd_stats_noalloc: C exceeds the built-in scratch (max 4096 channels)");
+    if (check_shape(M, C) != 0) return -1;
+    void* scratch = nullptr;
+    if (noalloc_scratch(&scratch) != 0) return -1;
+    // the array is shared and keeps the last call's contents: start from zero every time
+    TFOP_CUDA(cudaMemsetAsync(scratch, 0, kNoAllocScratchBytes, stream));
+    const dim3 nb = grid_for(M, C);
+    bn_fwd_stats_kernel<<<nb, kT, 0, stream>>>(
+        (const __nv_bfloat16*)x, M, C, (float*)scratch, ws_counter(scratch), gamma, beta,
+        param_dtype, running_mean, running_var, momentum, eps, scale_shift, save_mean,
+        save_invstd);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
