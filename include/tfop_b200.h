@@ -131,6 +131,24 @@ int tfop_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W
 int tfop_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C,
                           cudaStream_t stream);
 
+/* ---- K4/K5: parameter-server embedding over peer memory (csrc/ps.cu) ------
+ * The variable pull / gradient push + optimizer-on-PS of
+ * examples/v1/dist-mnist/dist_mnist.py:161-208. Row r lives on shard r % num_shards at local
+ * row r / num_shards; weight/accum are the shard bases as mapped in the calling process. */
+typedef struct tfop_ps_table {
+    float* weight[8];
+    float* accum[8];
+    int num_shards;
+    int dim;                  /* multiple of 4 */
+    long long rows_per_shard;
+} tfop_ps_table;
+int tfop_ps_gather(const tfop_ps_table* table, const void* ids_i64, size_t n_ids, void* out,
+                   int out_dtype, int max_blocks, cudaStream_t stream);
+int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_ids_i64,
+                         const void* seg_off_i64, const void* perm_i64, size_t n_uniq,
+                         const void* grad, int grad_dtype, float lr, float eps, float grad_scale,
+                         int max_blocks, cudaStream_t stream);
+
 /* ---- K7: tcgen05 / TMEM / TMA bf16 GEMM (csrc/gemm_tcgen05.cu) -----------
  * C[M,N] = epi(A[M,K] * B[N,K]^T + bias); the dense layers of
  * examples/v1/dist-mnist/dist_mnist.py:188-192. epilogue: 0 none, 1 bias,

@@ -232,3 +232,53 @@ def test_stem_space_to_depth_matches_7x7_conv(dev):
     torch.testing.assert_close(xs.float().cpu(), cpu.float(), rtol=0, atol=0)
     out = F.conv2d(xs.float(), stem_weight_s2d(w).float())
     torch.testing.assert_close(out, ref, rtol=2e-2, atol=0.3)
+
+
+# ----------------------------------------------------------------------------- PS embedding (K4/K5)
+@pytest.mark.parametrize("shards", [1, 2])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_ps_gather_and_fused_adagrad(dev, shards, dtype):
+    from tf_operator_b200.ops.ps_embedding import ShardedEmbedding
+    torch.manual_seed(9)
+    rows, dim = 1000, 64
+    emb = ShardedEmbedding.local(rows, dim, num_shards=shards, device=dev, lr=0.1, eps=1e-8,
+                                 initial_accumulator=0.1)
+    full = torch.empty(rows, dim, device=dev)
+    for s in range(shards):
+        full[s::shards] = emb.shards[s][: full[s::shards].shape[0]]
+    ids = torch.randint(0, rows, (4096,), device=dev)
+    ids[:50] = 7                                          # heavy duplicates
+    out = emb.gather(ids, dtype)
+    torch.testing.assert_close(out.float(), full[ids].to(dtype).float())
+    g = torch.randn(ids.numel(), dim, device=dev).to(dtype)
+    # reference: dedup (sum) then dense Adagrad on the touched rows
+    gsum = torch.zeros(rows, dim, device=dev).index_add_(0, ids, g.float())
+    touched = torch.zeros(rows, dtype=torch.bool, device=dev)
+    touched[ids] = True
+    acc = torch.full((rows, dim), 0.1, device=dev) + gsum * gsum
+    ref = full - 0.1 * gsum / (acc.sqrt() + 1e-8)
+    emb.push(ids, g)
+    torch.cuda.synchronize()
+    new = torch.empty(rows, dim, device=dev)
+    newacc = torch.empty(rows, dim, device=dev)
+    for s in range(shards):
+        new[s::shards] = emb.shards[s][: new[s::shards].shape[0]]
+        newacc[s::shards] = emb.accums[s][: new[s::shards].shape[0]]
+    tol = 2e-2 if dtype == torch.bfloat16 else 1e-4
+    torch.testing.assert_close(new[touched], ref[touched], rtol=tol, atol=tol)
+    torch.testing.assert_close(newacc[touched], acc[touched], rtol=tol, atol=tol * 10)
+    assert torch.equal(new[~touched], full[~touched])     # untouched rows are untouched
+
+
+def test_ps_lookup_autograd_pushes_on_backward(dev):
+    from tf_operator_b200.ops.ps_embedding import ShardedEmbedding
+    emb = ShardedEmbedding.local(100, 8, num_shards=2, device=dev, lr=0.5)
+    before = [s.clone() for s in emb.shards]
+    ids = torch.tensor([[1, 2], [2, 3]], device=dev)
+    y = emb.lookup(ids)
+    assert y.shape == (2, 2, 8) and y.requires_grad
+    y.sum().backward()
+    torch.cuda.synchronize()
+    changed = [not torch.equal(a, b) for a, b in zip(before, emb.shards)]
+    assert all(changed)
+    assert torch.equal(before[0][5], emb.shards[0][5])

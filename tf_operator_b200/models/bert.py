@@ -1,0 +1,109 @@
+"""BERT encoder (base / large) for the TFJob Chief+Workers data-parallel pre-training config
+(BASELINE.json config 3). Every projection / MLP GEMM runs on the hand-written tcgen05 kernel
+(ops/gemm.TcLinear, bias and GeLU fused in the epilogue); attention uses torch's fused SDPA
+(a library op, like the convolutions in the ResNet path).
+
+The reference has no BERT; the config is defined by BASELINE.json (bf16, seq 512, bucketed
+fused all-reduce).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops.gemm import TcLinear
+
+
+@dataclass
+class BertConfig:
+    vocab_size: int = 30528          # 30522 padded to a multiple of 64
+    hidden: int = 1024
+    layers: int = 24
+    heads: int = 16
+    intermediate: int = 4096
+    max_position: int = 512
+    type_vocab: int = 2
+    dropout: float = 0.0
+    eps: float = 1e-12
+
+    @classmethod
+    def large(cls):
+        return cls()
+
+    @classmethod
+    def base(cls):
+        return cls(hidden=768, layers=12, heads=12, intermediate=3072)
+
+    @classmethod
+    def tiny(cls):
+        return cls(vocab_size=1024, hidden=128, layers=2, heads=2, intermediate=512, max_position=128)
+
+
+class BertLayer(nn.Module):
+    def __init__(self, c: BertConfig):
+        super().__init__()
+        self.heads = c.heads
+        self.qkv = TcLinear(c.hidden, 3 * c.hidden)
+        self.proj = TcLinear(c.hidden, c.hidden)
+        self.ln1 = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.fc1 = TcLinear(c.hidden, c.intermediate, act="gelu")
+        self.fc2 = TcLinear(c.intermediate, c.hidden)
+        self.ln2 = nn.LayerNorm(c.hidden, eps=c.eps)
+
+    def forward(self, x, mask=None):
+        b, s, h = x.shape
+        qkv = self.qkv(x).view(b, s, 3, self.heads, h // self.heads).permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2], attn_mask=mask)
+        a = a.transpose(1, 2).reshape(b, s, h)
+        x = self.ln1(x + self.proj(a))
+        return self.ln2(x + self.fc2(self.fc1(x)))
+
+
+class BertForPreTraining(nn.Module):
+    """Masked-LM + next-sentence heads over the encoder; ``forward`` returns the summed loss."""
+
+    def __init__(self, c: BertConfig):
+        super().__init__()
+        self.cfg = c
+        self.tok = nn.Embedding(c.vocab_size, c.hidden)
+        self.pos = nn.Embedding(c.max_position, c.hidden)
+        self.typ = nn.Embedding(c.type_vocab, c.hidden)
+        self.ln = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.layers = nn.ModuleList(BertLayer(c) for _ in range(c.layers))
+        self.mlm_dense = TcLinear(c.hidden, c.hidden, act="gelu")
+        self.mlm_ln = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.mlm_bias = nn.Parameter(torch.zeros(c.vocab_size))
+        self.pooler = TcLinear(c.hidden, c.hidden)
+        self.nsp = TcLinear(c.hidden, 8)       # 2 classes, padded to 8 columns
+        self.apply(self._init)
+
+    @staticmethod
+    def _init(m):
+        if isinstance(m, (nn.Linear, nn.Embedding)):
+            nn.init.normal_(m.weight, std=0.02)
+        if isinstance(m, nn.Linear) and m.bias is not None:
+            nn.init.zeros_(m.bias)
+
+    def encode(self, ids, token_type=None):
+        b, s = ids.shape
+        pos = torch.arange(s, device=ids.device)
+        x = self.tok(ids) + self.pos(pos)[None] + self.typ(
+            token_type if token_type is not None else torch.zeros_like(ids))
+        x = self.ln(x)
+        for l in self.layers:
+            x = l(x)
+        return x
+
+    def forward(self, ids, mlm_labels, nsp_labels, token_type=None):
+        from ..ops.gemm import linear
+        x = self.encode(ids, token_type)
+        h = self.mlm_ln(self.mlm_dense(x))
+        logits = linear(h, self.tok.weight, self.mlm_bias)      # tied decoder, tcgen05 GEMM
+        mlm = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1),
+                              ignore_index=-100)
+        pooled = torch.tanh(self.pooler(x[:, 0]))
+        nsp = F.cross_entropy(self.nsp(pooled)[..., :2].float(), nsp_labels)
+        return mlm + nsp

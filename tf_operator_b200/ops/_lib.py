@@ -63,6 +63,9 @@ _SIGS = {
                                       c_void_p]),
     "tfop_maxpool3x3s2_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                       c_void_p]),
+    "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
+    "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
+                                     c_int, c_float, c_float, c_float, c_int, c_void_p]),
     "tfop_gemm_bf16_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                   c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
 }
@@ -73,6 +76,11 @@ EXTRA_SIGS: dict = {}
 
 class PackSeg(C.Structure):
     _fields_ = [("src", c_void_p), ("dst_off", C.c_ulonglong), ("n", C.c_ulonglong)]
+
+
+class PsTable(C.Structure):
+    _fields_ = [("weight", c_void_p * 8), ("accum", c_void_p * 8), ("num_shards", c_int),
+                ("dim", c_int), ("rows_per_shard", C.c_longlong)]
 
 
 class TfopError(RuntimeError):
