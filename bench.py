@@ -104,6 +104,8 @@ def main():
     ap.add_argument("--no-fused-bn", action="store_true")
     ap.add_argument("--no-s2d-stem", action="store_true",
                     help="feed the stem conv plain NHWC x3 input instead of the space-to-depth layout")
+    ap.add_argument("--no-nvls", action="store_true",
+                    help="use the P2P two-shot all-reduce even when NVLS multicast is available")
     ap.add_argument("--comm-blocks", type=int, default=32)
     ap.add_argument("--bucket-mb", type=int, default=16)
     ap.add_argument("--stock-mode", default="autocast", choices=["autocast", "purebf16"],
@@ -157,6 +159,7 @@ def main():
         return float(t.item())
 
     launches_per_step = 0
+    use_nvls = False
     if args.impl == "native":
         from tf_operator_b200.models.resnet import ResNet
         from tf_operator_b200.parallel.engine import DataParallelEngine
@@ -164,14 +167,17 @@ def main():
 
         model = ResNet(args.depth, fused=not args.no_fused_bn)
         comm = None
+        use_nvls = False
         if world > 1:
             nparam = sum((p.numel() + 7) // 8 * 8 for p in model.parameters())
             comm = SymmetricComm.from_torch_distributed(nparam * 2 + (8 << 20))
+            if not args.no_nvls:
+                use_nvls = comm.enable_nvls(nparam * 2 + (1 << 20))
         eng = DataParallelEngine(model, comm=comm, batch_size=B, image_size=S, lr=0.1,
                                  momentum=0.9, weight_decay=1e-4, graph=not args.no_graph,
                                  overlap=not args.no_overlap, comm_blocks=args.comm_blocks,
                                  bucket_bytes=args.bucket_mb << 20,
-                                 stem_s2d=not args.no_s2d_stem)
+                                 stem_s2d=not args.no_s2d_stem, use_nvls=use_nvls)
 
         def device_step():
             eng.run_device_step()
@@ -287,6 +293,9 @@ def main():
                        "fused_bn": args.impl == "native" and not args.no_fused_bn,
                        "stem": "space-to-depth 4x4 conv (same 7x7 parameters)"
                                if args.impl == "native" and not args.no_s2d_stem else "7x7/2",
+                       "allreduce": ("nvls multimem in place" if (args.impl == "native" and world > 1 and use_nvls)
+                                     else "p2p two-shot in place" if (args.impl == "native" and world > 1)
+                                     else None),
                        "stock_mode": args.stock_mode if args.impl == "stock" else None},
             "clocks": clocks,
             "e2e": {"value": round(gb / (e2e_ms / args.steps / 1e3), 2), "unit": "img/s",

@@ -51,7 +51,8 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     max_bytes = args.max_mb << 20
     comm = SymmetricComm.from_torch_distributed(2 * max_bytes + (1 << 20))
-    results = {"world": world, "rows": [], "note": "CUDA events, max over ranks; peer loads bypass local L2"}
+    nvls = comm.enable_nvls(max_bytes)
+    results = {"world": world, "nvls": bool(nvls), "rows": [], "note": "CUDA events, max over ranks; peer loads bypass local L2"}
     ok = True
     sizes = [1 << 10, 8 << 10, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20, max_bytes]
     # histogram shape of BASELINE config 5: 256 bins x 500 features x (g,h) fp32
@@ -91,6 +92,24 @@ def main():
         us = timed(lambda: comm.all_reduce(n, sym_off=0, scale=1.0, algo=TWO_SHOT), 20)
         row["twoshot_inplace"] = {"us": round(us, 2), "max_err": err,
                                   "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
+        if nvls:
+            out = torch.empty_like(x)
+            comm.all_reduce_nvls(n, inp=x, out=out, scale=1.0 / world)
+            torch.cuda.synchronize()
+            err = (out.float() - ref).abs().max().item()
+            gathered = [torch.empty_like(out) for _ in range(world)]
+            dist.all_gather(gathered, out)
+            same = all(torch.equal(g, gathered[0]) for g in gathered)
+            ok &= err < 0.05 and same
+            us = timed(lambda: comm.all_reduce_nvls(n, inp=x, out=out, scale=1.0 / world), 20)
+            row["nvls"] = {"us": round(us, 2), "max_err": err, "identical": same,
+                           "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
+            comm.nvls_view(n, torch.bfloat16).copy_(x)
+            dist.barrier()
+            torch.cuda.synchronize()
+            us = timed(lambda: comm.all_reduce_nvls(n, sym_off=0, scale=1.0), 20)
+            row["nvls_inplace"] = {"us": round(us, 2),
+                                   "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
         y = x.clone()
         us = timed(lambda: dist.all_reduce(y), 20)
         row["nccl"] = {"us": round(us, 2),
@@ -110,6 +129,13 @@ def main():
         us = timed(lambda: comm.all_reduce(hist_n, inp=h, out=hout, wire_dtype=torch.float32,
                                            algo=algo), 50)
         hrow[name] = {"us": round(us, 2), "max_err": err}
+    if nvls:
+        comm.all_reduce_nvls(hist_n, inp=h, out=hout, wire_dtype=torch.float32)
+        torch.cuda.synchronize()
+        err = (hout - href).abs().max().item()
+        ok &= err < 1e-3
+        us = timed(lambda: comm.all_reduce_nvls(hist_n, inp=h, out=hout, wire_dtype=torch.float32), 50)
+        hrow["nvls"] = {"us": round(us, 2), "max_err": err}
     hy = h.clone()
     hrow["nccl"] = {"us": round(timed(lambda: dist.all_reduce(hy), 50), 2)}
     results["histogram_f32"] = hrow

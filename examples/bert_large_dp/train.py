@@ -1,0 +1,90 @@
+#!/usr/bin/env python
+"""BERT-large data-parallel pre-training as TFJob replicas (BASELINE.json config 3: TFJob
+Chief + Workers, TF_CONFIG contract, bf16, bucketed fused all-reduce).
+
+Ranks come from TF_CONFIG (chief first, then workers; pkg/controller.v1/tensorflow/
+tensorflow.go:97-173). All projection / MLP GEMMs run on the hand-written tcgen05 kernel; the
+gradient buckets are all-reduced in place in symmetric memory as backward produces them.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+
+from tf_operator_b200.models.bert import BertConfig, BertForPreTraining  # noqa: E402
+from tf_operator_b200.parallel.engine import FlatDataParallel  # noqa: E402
+from tf_operator_b200.runtime.env import ReplicaContext  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="large", choices=["tiny", "base", "large"])
+    ap.add_argument("--batch-size", type=int, default=16, help="sequences per GPU")
+    ap.add_argument("--seq-len", type=int, default=512)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "nccl"])
+    args = ap.parse_args()
+
+    ctx = ReplicaContext.from_env()
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    cfg = getattr(BertConfig, args.model)()
+    torch.manual_seed(1234)
+    model = BertForPreTraining(cfg).to(dev).to(torch.bfloat16)
+    nparam = sum((p.numel() + 7) // 8 * 8 for p in model.parameters())
+    B, S = args.batch_size, min(args.seq_len, cfg.max_position)
+    g = torch.Generator(device=dev).manual_seed(10 + ctx.rank)
+    ids = torch.randint(0, cfg.vocab_size, (B, S), device=dev, generator=g)
+    labels = torch.where(torch.rand(B, S, device=dev, generator=g) < 0.15, ids, torch.full_like(ids, -100))
+    nsp = torch.randint(0, 2, (B,), device=dev, generator=g)
+
+    if args.impl == "nccl":
+        if ctx.world_size > 1:
+            ctx.init_process_group("nccl")
+            model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[0])
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.01, fused=True)
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            loss = model(ids, labels, nsp)
+            loss.backward()
+            opt.step()
+            return loss.detach()
+        launches = lambda: 0  # noqa: E731
+    else:
+        comm = ctx.symmetric_comm(nparam * 2 + (8 << 20)) if ctx.world_size > 1 else None
+        dp = FlatDataParallel(model, comm=comm, optimizer="adamw", lr=1e-4, weight_decay=0.01,
+                              bucket_bytes=64 << 20)
+
+        def step():
+            return dp.train_step(lambda: model(ids, labels, nsp))
+        launches = lambda: dp.kernel_launches_per_step  # noqa: E731
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    out = {"role": ctx.task_type, "rank": ctx.rank, "world": ctx.world_size, "impl": args.impl,
+           "model": f"bert-{args.model}", "params_M": round(nparam / 1e6, 1), "seq_len": S,
+           "per_gpu_batch": B, "ms_per_step": round(ms, 3),
+           "seq_per_s_job": round(B * ctx.world_size / ms * 1e3, 1), "loss": round(float(loss), 4),
+           "kernel_launches_per_step": launches()}
+    print(json.dumps(out), flush=True)
+    time.sleep(0.5)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

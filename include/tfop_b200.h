@@ -59,6 +59,23 @@ int tfop_allreduce_emulated(tfop_comm** comms, int world, const void* const* ins
                             cudaStream_t stream);
 int tfop_allreduce_set_oneshot_max_bytes(size_t bytes);
 
+/* ---- K2: NVLS (in-switch) all-reduce (csrc/nvls.cu) ------------------------
+ * Same reference call site as tfop_allreduce. Set-up: rank 0 tfop_nvls_create -> send the fd
+ * to the other ranks (SCM_RIGHTS) -> they tfop_nvls_import; all: tfop_nvls_add_device,
+ * barrier, tfop_nvls_bind, barrier. Probe with tfop_nvls_supported first. */
+int tfop_nvls_supported(int* out);
+int tfop_nvls_round_size(int world, size_t bytes, size_t* out);
+int tfop_nvls_create(tfop_comm* c, size_t bytes, int* out_fd);
+int tfop_nvls_import(tfop_comm* c, size_t bytes, int fd);
+int tfop_nvls_add_device(tfop_comm* c);
+int tfop_nvls_bind(tfop_comm* c);
+void* tfop_nvls_local_ptr(tfop_comm* c);
+size_t tfop_nvls_bytes(tfop_comm* c);
+int tfop_allreduce_nvls(tfop_comm* c, const void* in, int in_dtype, void* out, int out_dtype,
+                        int wire_dtype, size_t n, size_t sym_off, float scale, int max_blocks,
+                        cudaStream_t stream);
+int tfop_nvls_destroy(tfop_comm* c);
+
 /* ---- fused flat-buffer optimizers (csrc/optim.cu) ------------------------
  * The optimizer step that follows the gradient exchange in
  * examples/v1/dist-mnist/dist_mnist.py:194-208. hp_dev: device float[8] =
@@ -148,6 +165,13 @@ int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_ids_i64,
                          const void* seg_off_i64, const void* perm_i64, size_t n_uniq,
                          const void* grad, int grad_dtype, float lr, float eps, float grad_scale,
                          int max_blocks, cudaStream_t stream);
+
+/* ---- gradient histogram build for boosted trees (csrc/hist.cu) --------------
+ * The per-worker step in front of the rabit histogram all-reduce of
+ * examples/xgboost/xgboostjob.yaml:19-25. bins: uint8 [rows, F]; out: fp32 [F][256][2],
+ * zeroed by the caller; row_idx: int32 rows of the node, or NULL for all rows. */
+int tfop_hist_build(const void* bins_u8, const float* grad, const float* hess,
+                    const int* row_idx, size_t n_rows, int F, float* out, cudaStream_t stream);
 
 /* ---- K7: tcgen05 / TMEM / TMA bf16 GEMM (csrc/gemm_tcgen05.cu) -----------
  * C[M,N] = epi(A[M,K] * B[N,K]^T + bias); the dense layers of

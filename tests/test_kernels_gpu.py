@@ -282,3 +282,20 @@ def test_ps_lookup_autograd_pushes_on_backward(dev):
     changed = [not torch.equal(a, b) for a, b in zip(before, emb.shards)]
     assert all(changed)
     assert torch.equal(before[0][5], emb.shards[0][5])
+
+
+# ----------------------------------------------------------------------------- boosting histograms
+@pytest.mark.parametrize("rows,feats", [(10000, 500), (3000, 13)])
+def test_hist_build_matches_index_add(dev, rows, feats):
+    from tf_operator_b200.ops.hist import build_histogram
+    torch.manual_seed(10)
+    bins = torch.randint(0, 256, (rows, feats), dtype=torch.uint8, device=dev)
+    g = torch.randn(rows, device=dev)
+    h = torch.rand(rows, device=dev)
+    ref = build_histogram(bins.cpu(), g.cpu(), h.cpu())
+    got = build_histogram(bins, g, h)
+    torch.testing.assert_close(got.cpu(), ref, rtol=1e-3, atol=1e-3)
+    idx = torch.randperm(rows, device=dev)[: rows // 3].int()
+    ref2 = build_histogram(bins.cpu(), g.cpu(), h.cpu(), idx.cpu())
+    got2 = build_histogram(bins, g, h, idx)
+    torch.testing.assert_close(got2.cpu(), ref2, rtol=1e-3, atol=1e-3)

@@ -68,6 +68,8 @@ class ManagerOptions:
     health_probe_bind_address: str = ""  # ":8081"
     fail_invalid_spec: bool = False      # legacy tf-operator.v1 behaviour
     check_crd: bool = False              # legacy: refuse to start without the TFJob CRD
+    qps: float = 0.0                     # >0: client-go style write throttle (legacy default 5)
+    burst: int = 10
 
 
 class Manager:
@@ -92,6 +94,18 @@ class Manager:
             q = RateLimitingQueue(name=kind)
             r = RECONCILERS[kind](store, config=cfg, workqueue=q, metrics=self.metrics)
             r.fail_invalid_spec = self.opt.fail_invalid_spec
+            if self.opt.qps > 0:
+                from ..engine.ratelimit import ThrottledControl, TokenBucket
+                if not hasattr(self, "_bucket"):
+                    self._bucket = TokenBucket(self.opt.qps, self.opt.burst)
+                r.pod_control = ThrottledControl(r.pod_control, self._bucket)
+                r.service_control = ThrottledControl(r.service_control, self._bucket)
+                _orig = r.update_job_status_in_api_server
+
+                def _throttled_status(job, status, _orig=_orig):
+                    self._bucket.accept()
+                    return _orig(job, status)
+                r.update_job_status_in_api_server = _throttled_status
             self.queues[kind] = q
             self.reconcilers[kind] = r
         self._by_plural = {r.info.plural: k for k, r in self.reconcilers.items()}

@@ -63,6 +63,19 @@ _SIGS = {
                                       c_void_p]),
     "tfop_maxpool3x3s2_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                       c_void_p]),
+    "tfop_nvls_supported": (c_int, [C.POINTER(c_int)]),
+    "tfop_nvls_round_size": (c_int, [c_int, c_size_t, C.POINTER(c_size_t)]),
+    "tfop_nvls_create": (c_int, [c_void_p, c_size_t, C.POINTER(c_int)]),
+    "tfop_nvls_import": (c_int, [c_void_p, c_size_t, c_int]),
+    "tfop_nvls_add_device": (c_int, [c_void_p]),
+    "tfop_nvls_bind": (c_int, [c_void_p]),
+    "tfop_nvls_local_ptr": (c_void_p, [c_void_p]),
+    "tfop_nvls_bytes": (c_size_t, [c_void_p]),
+    "tfop_nvls_destroy": (c_int, [c_void_p]),
+    "tfop_allreduce_nvls": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_size_t,
+                                    c_size_t, c_float, c_int, c_void_p]),
+    "tfop_hist_build": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_void_p,
+                                c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
                                      c_int, c_float, c_float, c_float, c_int, c_void_p]),

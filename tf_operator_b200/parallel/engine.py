@@ -42,60 +42,51 @@ class StepHandle:
         return float(self._host.item())
 
 
-class DataParallelEngine:
+class FlatDataParallel:
+    """Model-agnostic core: flat parameter buffers, bucketed gradient exchange overlapped with
+    backward, one fused optimizer kernel. ``train_step(closure)`` runs one eager step for any
+    model (BERT, wide-and-deep, ...); DataParallelEngine adds the image pipeline + CUDA graph.
+    """
+
     def __init__(self, model: nn.Module, *, comm: Optional[SymmetricComm] = None,
-                 batch_size: int, image_size: int = 224, channels: int = 3,
-                 lr: float = 0.1, momentum: float = 0.9, weight_decay: float = 1e-4,
-                 nesterov: bool = False, bucket_bytes: int = 16 << 20, graph: bool = True,
-                 overlap: bool = True, comm_blocks: int = 32,
-                 loss_fn: Optional[Callable] = None, device: Optional[torch.device] = None,
-                 label_smoothing: float = 0.0, stem_s2d: bool = False):
+                 optimizer: str = "sgd", lr: float = 0.1, momentum: float = 0.9,
+                 weight_decay: float = 1e-4, nesterov: bool = False, betas=(0.9, 0.999),
+                 eps: float = 1e-8, bucket_bytes: int = 16 << 20, overlap: bool = True,
+                 comm_blocks: int = 32, device: Optional[torch.device] = None,
+                 channels_last: bool = False, use_nvls: bool = False):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.comm = comm
         self.world = comm.world if comm is not None else 1
-        self.batch_size, self.image_size, self.channels = batch_size, image_size, channels
-        self.loss_fn = loss_fn or (lambda out, y: F.cross_entropy(
-            out.float(), y, label_smoothing=label_smoothing))
         self.overlap = overlap and self.world > 1
         self.comm_blocks = comm_blocks
-        self.kernel_launches_per_step = 0
-
-        model.to(self.device).to(memory_format=torch.channels_last)
+        self.optimizer = optimizer
+        self.nesterov = nesterov
+        self.use_nvls = use_nvls and comm is not None and getattr(comm, "nvls_bytes", 0) > 0
+        model.to(self.device)
+        if channels_last:
+            model.to(memory_format=torch.channels_last)
         self.model = model
-        grad_buf = None
         total = sum((p.numel() + 7) // 8 * 8 for p in model.parameters() if p.requires_grad)
+        grad_buf = None
         if comm is not None:
-            assert comm.nbytes >= total * 2, "symmetric buffer too small for the gradient bucket"
-            grad_buf = comm.view(0, total, torch.bfloat16)
+            if self.use_nvls:
+                assert comm.nvls_bytes >= total * 2, "NVLS buffer too small for the gradient bucket"
+                grad_buf = comm.nvls_view(total, torch.bfloat16)
+            else:
+                assert comm.nbytes >= total * 2, "symmetric buffer too small for the gradient bucket"
+                grad_buf = comm.view(0, total, torch.bfloat16)
         self.flat = FlatParams(model, self.device, grad_buffer=grad_buf, bucket_bytes=bucket_bytes)
         self.mom = torch.zeros(self.flat.total, dtype=torch.float32, device=self.device)
+        self.mom2 = torch.zeros(self.flat.total, dtype=torch.float32, device=self.device) \
+            if optimizer == "adamw" else None
         self.hp = torch.zeros(8, dtype=torch.float32, device=self.device)
-        self._hp_host = torch.tensor([lr, momentum, weight_decay, 1.0, 0.9, 0.999, 1e-8, 0.0],
+        self._hp_host = torch.tensor([lr, momentum, weight_decay, 1.0, betas[0], betas[1], eps, 0.0],
                                      dtype=torch.float32).pin_memory()
         self.hp.copy_(self._hp_host)
-        self.nesterov = nesterov
-
-        # static device inputs / outputs (graph-friendly) + double-buffered staging
-        shp = (batch_size, image_size, image_size, channels)
-        self.x_u8 = torch.zeros(shp, dtype=torch.uint8, device=self.device)
-        self.stem_s2d = stem_s2d and channels == 3 and image_size % 2 == 0
-        xshp = (batch_size, image_size // 2 + 3, image_size // 2 + 3, 16) if self.stem_s2d else shp
-        self.x_bf16 = torch.zeros(xshp, dtype=torch.bfloat16, device=self.device)
-        self.labels = torch.zeros(batch_size, dtype=torch.int64, device=self.device)
-        self.loss_dev = torch.zeros((), dtype=torch.float32, device=self.device)
-        self._stage_x = [torch.zeros_like(self.x_u8) for _ in range(2)]
-        self._stage_y = [torch.zeros_like(self.labels) for _ in range(2)]
-        self._stage_ready = [torch.cuda.Event() for _ in range(2)]
-        self._stage_free = [torch.cuda.Event() for _ in range(2)]
-        self._host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
-        self._slot = 0
-        self._prefetched = None
-        self.copy_stream = torch.cuda.Stream(device=self.device)
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
-        self.main_stream = torch.cuda.Stream(device=self.device)
-        self._graph: Optional[torch.cuda.CUDAGraph] = None
-        self._use_graph = graph
+        self.kernel_launches_per_step = 0
         self._steps = 0
+        self._in_backward = False
         self._hook_lock = threading.Lock()
         self._install_hooks()
 
@@ -123,17 +114,104 @@ class DataParallelEngine:
         return hook
 
     def _reduce_bucket(self, b, stream):
-        srcs = [s.param.grad for s in b.slots]
-        offs = [s.offset for s in b.slots]
+        srcs = [s.param.grad for s in b.slots if s.param.grad is not None]
+        offs = [s.offset for s in b.slots if s.param.grad is not None]
         fopt.multi_pack_bf16(srcs, offs, self.flat.grads, 1.0, stream)
         if self.world > 1:
             # in place on the symmetric gradient bucket: sum over ranks * 1/world
-            self.comm.all_reduce(b.hi - b.lo, sym_off=b.lo * 2, wire_dtype=torch.bfloat16,
-                                 scale=1.0 / self.world, algo=TWO_SHOT,
-                                 max_blocks=self.comm_blocks, stream=stream)
+            if self.use_nvls:
+                # reduced inside the NVSwitch, in place on the multicast-bound gradient bucket
+                self.comm.all_reduce_nvls(b.hi - b.lo, sym_off=b.lo * 2, scale=1.0 / self.world,
+                                          max_blocks=self.comm_blocks, stream=stream)
+            else:
+                self.comm.all_reduce(b.hi - b.lo, sym_off=b.lo * 2, wire_dtype=torch.bfloat16,
+                                     scale=1.0 / self.world, algo=TWO_SHOT,
+                                     max_blocks=self.comm_blocks, stream=stream)
 
-    # ------------------------------------------------------------------ step
-    _in_backward = False
+    # ------------------------------------------------------------------ step pieces
+    def _begin(self):
+        for p in self.model.parameters():
+            p.grad = None
+        for b in self.flat.buckets:
+            b.pending = len(b.slots)
+
+    def _backward_and_update(self, loss):
+        self._in_backward = True
+        try:
+            loss.backward()
+        finally:
+            self._in_backward = False
+        cur = torch.cuda.current_stream()
+        if self.overlap:
+            # buckets whose last gradient never arrived (unused parameters) are reduced now
+            cur.wait_stream(self.comm_stream)
+            for b in self.flat.buckets:
+                if b.pending > 0:
+                    self._reduce_bucket(b, cur)
+        else:
+            for b in self.flat.buckets:
+                self._reduce_bucket(b, cur)
+        if self.optimizer == "adamw":
+            fopt.adamw_(self.flat.master, self.mom, self.mom2, self.flat.grads, self.flat.weights,
+                        self.flat.n_decay, self.hp, cur)
+        else:
+            fopt.sgd_momentum_(self.flat.master, self.mom, self.flat.grads, self.flat.weights,
+                               self.flat.n_decay, self.hp, self.nesterov, cur)
+
+    def train_step(self, closure) -> torch.Tensor:
+        """One eager step: ``closure()`` returns the loss; returns the detached loss tensor."""
+        from ..ops import _lib
+        l0 = _lib.launches_total()
+        if self.optimizer == "adamw":
+            self._hp_host[7] = float(self._steps + 1)
+            self.hp.copy_(self._hp_host, non_blocking=True)
+        self._begin()
+        loss = closure()
+        self._backward_and_update(loss)
+        self.kernel_launches_per_step = _lib.launches_total() - l0
+        self._steps += 1
+        return loss.detach()
+
+    def set_lr(self, lr: float):
+        self._hp_host[0] = lr
+        self.hp.copy_(self._hp_host, non_blocking=True)
+
+
+class DataParallelEngine(FlatDataParallel):
+    def __init__(self, model: nn.Module, *, comm: Optional[SymmetricComm] = None,
+                 batch_size: int, image_size: int = 224, channels: int = 3,
+                 lr: float = 0.1, momentum: float = 0.9, weight_decay: float = 1e-4,
+                 nesterov: bool = False, bucket_bytes: int = 16 << 20, graph: bool = True,
+                 overlap: bool = True, comm_blocks: int = 32,
+                 loss_fn: Optional[Callable] = None, device: Optional[torch.device] = None,
+                 label_smoothing: float = 0.0, stem_s2d: bool = False, use_nvls: bool = False):
+        super().__init__(model, comm=comm, optimizer="sgd", lr=lr, momentum=momentum,
+                         weight_decay=weight_decay, nesterov=nesterov, bucket_bytes=bucket_bytes,
+                         overlap=overlap, comm_blocks=comm_blocks, device=device,
+                         channels_last=True, use_nvls=use_nvls)
+        self.batch_size, self.image_size, self.channels = batch_size, image_size, channels
+        self.loss_fn = loss_fn or (lambda out, y: F.cross_entropy(
+            out.float(), y, label_smoothing=label_smoothing))
+
+        # static device inputs / outputs (graph-friendly) + double-buffered staging
+        shp = (batch_size, image_size, image_size, channels)
+        self.x_u8 = torch.zeros(shp, dtype=torch.uint8, device=self.device)
+        self.stem_s2d = stem_s2d and channels == 3 and image_size % 2 == 0
+        xshp = (batch_size, image_size // 2 + 3, image_size // 2 + 3, 16) if self.stem_s2d else shp
+        self.x_bf16 = torch.zeros(xshp, dtype=torch.bfloat16, device=self.device)
+        self.labels = torch.zeros(batch_size, dtype=torch.int64, device=self.device)
+        self.loss_dev = torch.zeros((), dtype=torch.float32, device=self.device)
+        self._stage_x = [torch.zeros_like(self.x_u8) for _ in range(2)]
+        self._stage_y = [torch.zeros_like(self.labels) for _ in range(2)]
+        self._stage_ready = [torch.cuda.Event() for _ in range(2)]
+        self._stage_free = [torch.cuda.Event() for _ in range(2)]
+        self._host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self._slot = 0
+        self._prefetched = None
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.main_stream = torch.cuda.Stream(device=self.device)
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._use_graph = graph
 
     def _body(self):
         """fwd + bwd + gradient exchange + optimizer on the current stream."""
@@ -143,26 +221,11 @@ class DataParallelEngine:
             x = preproc.stem_space_to_depth(self.x_u8, self.x_bf16)
         else:
             x = preproc.u8_to_bf16_normalize(self.x_u8, self.x_bf16)
-        for p in self.model.parameters():
-            p.grad = None
-        for b in self.flat.buckets:
-            b.pending = len(b.slots)
+        self._begin()
         out = self.model(x)
         loss = self.loss_fn(out, self.labels)
         self.loss_dev.copy_(loss.detach())
-        self._in_backward = True
-        try:
-            loss.backward()
-        finally:
-            self._in_backward = False
-        cur = torch.cuda.current_stream()
-        if self.overlap:
-            cur.wait_stream(self.comm_stream)
-        else:
-            for b in self.flat.buckets:
-                self._reduce_bucket(b, cur)
-        fopt.sgd_momentum_(self.flat.master, self.mom, self.flat.grads, self.flat.weights,
-                           self.flat.n_decay, self.hp, self.nesterov, cur)
+        self._backward_and_update(loss)
         self.kernel_launches_per_step = _lib.launches_total() - l0
         if self._steps == 0 and not torch.cuda.is_current_stream_capturing():
             bad = self.flat.check_grad_layouts()

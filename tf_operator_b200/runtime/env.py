@@ -130,9 +130,21 @@ class ReplicaContext:
             rank=self.rank, world_size=self.world_size,
             timeout=datetime.timedelta(seconds=timeout_s))
 
-    def symmetric_comm(self, nbytes: int, tag: str = "comm0"):
+    def symmetric_comm(self, nbytes: int, tag: str = "comm0", nvls_bytes: int = 0):
         """Symmetric peer-memory communicator; handles are exchanged through the launcher's
-        rendezvous store when there is one, else through torch.distributed."""
+        rendezvous store when there is one, else through torch.distributed. ``nvls_bytes`` > 0
+        additionally binds a multicast (NVLS) buffer of that size when the box supports it
+        (``comm.nvls_bytes`` is 0 otherwise)."""
+        comm = self._symmetric_comm(nbytes, tag)
+        comm.nvls_bytes = 0
+        if nvls_bytes and self.world_size > 1:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                self.init_process_group("gloo")
+            comm.enable_nvls(nvls_bytes)
+        return comm
+
+    def _symmetric_comm(self, nbytes: int, tag: str):
         from .symm import SymmetricComm
         addr = self.raw.get("TFOP_RENDEZVOUS")
         if addr and self.world_size > 1:

@@ -119,6 +119,93 @@ class SymmetricComm:
             _lib.dtype_tag(wire_dtype), n, sym_off, float(scale), algo, max_blocks,
             _lib.stream_handle(stream)), "allreduce")
 
+    # ---- NVLS (multicast) ------------------------------------------------------
+    @staticmethod
+    def nvls_supported() -> bool:
+        flag = C.c_int(0)
+        rc = _lib.load().tfop_nvls_supported(C.byref(flag))
+        return rc == 0 and bool(flag.value)
+
+    def enable_nvls(self, nbytes: int, group=None) -> bool:
+        """Create/import the multicast object, bind this rank's memory and map both views.
+        The multicast fd travels from rank 0 to the others over a Unix socket (SCM_RIGHTS);
+        torch.distributed provides the barriers. Returns False when the box has no NVLS."""
+        import os
+        import socket
+        import time
+
+        import torch.distributed as dist
+        self.nvls_bytes = 0
+        if self.world == 1 or not self.nvls_supported():
+            return False
+        lib = self._lib
+        cpu_group = dist.get_backend(group) == "gloo"
+        ok = torch.tensor([1], device="cpu" if cpu_group else self.device)
+        name = [f"\0tfop-nvls-{os.getpid()}-{id(self) & 0xffff}"]
+        dist.broadcast_object_list(name, src=0, group=group)
+        with torch.cuda.device(self.device):
+            if self.rank == 0:
+                fd = C.c_int(-1)
+                rc = lib.tfop_nvls_create(self._h, nbytes, C.byref(fd))
+                if rc != 0:
+                    ok[0] = 0
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(name[0])
+                srv.listen(self.world)
+                dist.barrier(group=group)            # listening
+                for _ in range(self.world - 1):
+                    conn, _ = srv.accept()
+                    if rc == 0:
+                        socket.send_fds(conn, [b"fd"], [fd.value])
+                    else:
+                        conn.sendall(b"no")
+                    conn.close()
+                srv.close()
+                if rc == 0:
+                    os.close(fd.value)
+            else:
+                dist.barrier(group=group)
+                cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                for _ in range(200):
+                    try:
+                        cli.connect(name[0])
+                        break
+                    except OSError:
+                        time.sleep(0.05)
+                msg, fds, _, _ = socket.recv_fds(cli, 16, 1)
+                cli.close()
+                if not fds or lib.tfop_nvls_import(self._h, nbytes, fds[0]) != 0:
+                    ok[0] = 0
+                for f in fds:
+                    os.close(f)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                return False
+            _lib.check(lib.tfop_nvls_add_device(self._h), "nvls_add_device")
+            dist.barrier(group=group)
+            _lib.check(lib.tfop_nvls_bind(self._h), "nvls_bind")
+            dist.barrier(group=group)
+        self.nvls_bytes = lib.tfop_nvls_bytes(self._h)
+        return True
+
+    def nvls_view(self, numel: int, dtype: torch.dtype, byte_off: int = 0) -> torch.Tensor:
+        """This rank's copy of the multicast-bound buffer."""
+        p = self._lib.tfop_nvls_local_ptr(self._h)
+        es = torch.empty((), dtype=dtype).element_size()
+        buf = tensor_from_ptr(p, self.nvls_bytes, self.device, owner=self)
+        return buf[byte_off: byte_off + numel * es].view(dtype)
+
+    def all_reduce_nvls(self, n: int, *, inp: Optional[torch.Tensor] = None,
+                        out: Optional[torch.Tensor] = None, sym_off: int = 0,
+                        wire_dtype: torch.dtype = torch.bfloat16, scale: float = 1.0,
+                        max_blocks: int = 0, stream=None) -> None:
+        """All-reduce reduced inside the NVSwitch (multimem.ld_reduce / multimem.st)."""
+        _lib.check(self._lib.tfop_allreduce_nvls(
+            self._h, _lib.ptr(inp), _lib.dtype_tag(inp.dtype) if inp is not None else 0,
+            _lib.ptr(out), _lib.dtype_tag(out.dtype) if out is not None else 0,
+            _lib.dtype_tag(wire_dtype), n, sym_off, float(scale), max_blocks,
+            _lib.stream_handle(stream)), "allreduce_nvls")
+
     def check_error(self) -> bool:
         flag = C.c_int(0)
         _lib.check(self._lib.tfop_comm_check_error(self._h, C.byref(flag)), "comm_check_error")
@@ -127,6 +214,8 @@ class SymmetricComm:
     def close(self):
         if self._h:
             self._views.clear()
+            if getattr(self, "nvls_bytes", 0):
+                self._lib.tfop_nvls_destroy(self._h)
             self._lib.tfop_comm_destroy(self._h)
             self._h = None
 
