@@ -66,7 +66,11 @@ def main():
                 status = types[-1]
                 break
             time.sleep(0.05)
-        logs = cli.get_logs(name, master=False) or {}
+        # read the log files directly: with cleanPodPolicy All/Running the pods may be gone already
+        logs = {}
+        log_root = cl.kubelet._log_dir / job["metadata"].get("namespace", "default")
+        for pod_dir in sorted(log_root.glob(name + "-*")):
+            logs[pod_dir.name] = "".join(f.read_text(errors="replace") for f in sorted(pod_dir.glob("*.log")))
         result = {"job": name, "kind": job["kind"], "status": status or "Timeout",
                   "launch_to_running_s": running_at, "wall_s": round(time.time() - t_create, 2)}
         print(json.dumps(result))
