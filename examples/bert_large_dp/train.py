@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "nccl"])
+    ap.add_argument("--no-graph", action="store_true", help="run eager instead of one CUDA graph per step")
     args = ap.parse_args()
 
     ctx = ReplicaContext.from_env()
@@ -62,8 +63,31 @@ def main():
         dp = FlatDataParallel(model, comm=comm, optimizer="adamw", lr=1e-4, weight_decay=0.01,
                               bucket_bytes=64 << 20)
 
-        def step():
+        graph = {"g": None, "loss": None}
+
+        def eager():
             return dp.train_step(lambda: model(ids, labels, nsp))
+
+        def step():
+            if args.no_graph:
+                return eager()
+            if graph["g"] is None:
+                side = torch.cuda.Stream()
+                with torch.cuda.stream(side):
+                    for _ in range(2):
+                        eager()
+                side.synchronize()
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    graph["loss"] = eager()
+                graph["g"] = g
+            # the AdamW step counter lives in device memory: bump it, then replay
+            dp._hp_host[7] = float(dp._steps + 1)
+            dp.hp.copy_(dp._hp_host, non_blocking=True)
+            dp._steps += 1
+            graph["g"].replay()
+            return graph["loss"]
         launches = lambda: dp.kernel_launches_per_step  # noqa: E731
 
     for _ in range(args.warmup):

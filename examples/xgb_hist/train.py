@@ -57,7 +57,7 @@ def main():
         if args.impl == "nccl":
             ctx.init_process_group("nccl")
         else:
-            comm = ctx.symmetric_comm(2 * max_nodes * hist_n * 4 + (1 << 20),
+            comm = ctx.symmetric_comm(2 * max_nodes * hist_n * 4 + (2 << 20),
                                       nvls_bytes=max_nodes * hist_n * 4)
 
     g = torch.Generator(device=dev).manual_seed(100 + rank)
@@ -65,7 +65,9 @@ def main():
     w_true = torch.randn(args.features, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
     y = ((bins[:, :32].float() - 127.5) @ w_true[:32] + 40 * torch.randn(args.rows, device=dev, generator=g) > 0).float()
     pred = torch.zeros(args.rows, device=dev)
+    sync_buf = torch.zeros(8, device=dev)
     ar_us, ar_calls = 0.0, 0
+    by_level = {}
     t0 = time.time()
     for tree in range(args.trees):
         p = torch.sigmoid(pred)
@@ -84,19 +86,29 @@ def main():
                 idx = (node == k).nonzero().flatten().int()
                 build_histogram(bins, grad, hess, idx, out=hist[k])
             if world > 1:
+                # line the ranks up first so the timing below is the all-reduce, not the skew
+                # between the ranks' histogram builds
+                if comm is not None:
+                    comm.all_reduce(8, inp=sync_buf, out=sync_buf, wire_dtype=torch.float32)
+                else:
+                    torch.distributed.all_reduce(sync_buf)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 flat = hist.view(-1)
                 if comm is not None and comm.nvls_bytes:
                     comm.all_reduce_nvls(flat.numel(), wire_dtype=torch.float32)
                 elif comm is not None:
-                    comm.all_reduce(flat.numel(), inp=flat, out=flat, wire_dtype=torch.float32)
+                    comm.all_reduce(flat.numel(), inp=flat, out=flat, wire_dtype=torch.float32,
+                                    sym_off=1 << 20)
                 else:
                     torch.distributed.all_reduce(flat)
                 e1.record()
                 torch.cuda.synchronize()
-                ar_us += e0.elapsed_time(e1) * 1e3
-                ar_calls += 1
+                dt_us = e0.elapsed_time(e1) * 1e3
+                if tree > 0:                      # tree 0 carries one-time set-up costs
+                    ar_us += dt_us
+                    ar_calls += 1
+                    by_level.setdefault(n_nodes, []).append(dt_us)
             if level == args.depth - 1:
                 tot = hist[:, 0].sum(1)                       # [nodes, 2]
                 leaf_value[:n_nodes] = -tot[:, 0] / (tot[:, 1] + 1.0)
@@ -115,7 +127,9 @@ def main():
            "features": args.features, "trees": args.trees, "depth": args.depth,
            "logloss": round(loss, 4), "accuracy": round(acc, 4), "wall_s": round(dt, 3),
            "hist_allreduce_calls": ar_calls,
-           "hist_allreduce_us_mean": round(ar_us / ar_calls, 1) if ar_calls else None}
+           "hist_allreduce_us_mean": round(ar_us / ar_calls, 1) if ar_calls else None,
+           "hist_allreduce_us_by_level": {str(k): round(sum(v) / len(v), 1) for k, v in by_level.items()},
+           "nvls": bool(comm is not None and comm.nvls_bytes)}
     print(json.dumps(out), flush=True)
     if comm is not None:
         time.sleep(0.5)

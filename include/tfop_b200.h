@@ -181,6 +181,22 @@ int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias, i
                       int M, int N, int K, int lda, int ldb, int ldc, int out_dtype,
                       int epilogue, int tile_n, cudaStream_t stream);
 
+/* ---- fused GEMM -> reduce-scatter -> all-gather (csrc/gemm_allreduce.cu) ---------
+ * Gradient GEMM + NCCL all-reduce of keras-API/multi_worker_strategy-with-keras.py:76-77,
+ * 117-120 as ONE kernel over peer memory: out[M,N] (bf16, in every rank's symmetric buffer at
+ * out_off, row pitch ldo) = scale * sum_r A_r[M,K] * B_r[N,K]^T. The workspace at ws_off
+ * (tfop_gemm_allreduce_workspace_bytes, zero-initialised once) holds partial-tile slots and
+ * counters. */
+size_t tfop_gemm_allreduce_workspace_bytes(int M, int N, int world);
+int tfop_gemm_allreduce_set_timeout(long long cycles);
+int tfop_gemm_allreduce_bf16_tn(tfop_comm* c, const void* A, const void* B, int M, int N, int K,
+                                int lda, int ldb, int ldo, float scale, size_t ws_off,
+                                size_t out_off, int max_ctas, cudaStream_t stream);
+int tfop_gemm_allreduce_emulated(tfop_comm** comms, int world, const void* const* As,
+                                 const void* const* Bs, int M, int N, int K, int lda, int ldb,
+                                 int ldo, float scale, size_t ws_off, size_t out_off,
+                                 cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

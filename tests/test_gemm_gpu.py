@@ -81,3 +81,34 @@ def test_tc_linear_forward_backward(gemm_ok):
     torch.testing.assert_close(x.grad.float(), xr.grad, rtol=5e-2, atol=1e-3)
     torch.testing.assert_close(lin.weight.grad.float(), wr.grad, rtol=5e-2, atol=1e-3)
     torch.testing.assert_close(lin.bias.grad.float(), br.grad, rtol=5e-2, atol=1e-3)
+
+
+FUSED_PROBE = r"""
+import torch
+from tf_operator_b200.runtime.symm import SymmetricComm, gemm_all_reduce_emulated
+torch.manual_seed(0)
+W, M, N, K = 2, 384, 520, 256
+ws = SymmetricComm.gemm_allreduce_workspace_bytes(M, N, W)
+comms = SymmetricComm.emulated(W, ws + M * N * 2 + 4096)
+a = [torch.randn(M, K, device='cuda').bfloat16() for _ in range(W)]
+b = [torch.randn(N, K, device='cuda').bfloat16() for _ in range(W)]
+for it in range(2):
+    outs = gemm_all_reduce_emulated(comms, a, b, ws_off=0, out_off=ws, scale=0.5)
+    torch.cuda.synchronize()
+assert not comms[0].check_error()
+ref = sum(x.float() @ y.float().t() for x, y in zip(a, b)) * 0.5
+err = max((o.float() - ref).abs().max().item() for o in outs)
+print('maxerr', err, 'ref max', ref.abs().max().item())
+assert err < 0.02 * ref.abs().max().item() + 0.5, err
+assert torch.equal(outs[0], outs[1])
+"""
+
+
+def test_fused_gemm_allreduce_emulated(gemm_ok):
+    """GEMM -> reduce-scatter -> all-gather in one kernel, 2 emulated ranks on one GPU; run in a
+    subprocess with a hard timeout because its ranks wait on each other."""
+    try:
+        res = subprocess.run([sys.executable, "-c", FUSED_PROBE], capture_output=True, text=True, timeout=180)
+    except subprocess.TimeoutExpired:
+        pytest.fail("fused GEMM+all-reduce probe timed out")
+    assert res.returncode == 0, f"{res.stdout}\n{res.stderr[-3000:]}"

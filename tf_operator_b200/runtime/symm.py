@@ -206,6 +206,29 @@ class SymmetricComm:
             _lib.dtype_tag(wire_dtype), n, sym_off, float(scale), max_blocks,
             _lib.stream_handle(stream)), "allreduce_nvls")
 
+    # ---- fused GEMM + all-reduce --------------------------------------------------
+    @staticmethod
+    def gemm_allreduce_workspace_bytes(m: int, n: int, world: int) -> int:
+        return _lib.load().tfop_gemm_allreduce_workspace_bytes(m, n, world)
+
+    def gemm_all_reduce(self, a: torch.Tensor, b: torch.Tensor, *, ws_off: int, out_off: int,
+                        ldo: Optional[int] = None, scale: float = 1.0, max_ctas: int = 0,
+                        stream=None) -> torch.Tensor:
+        """out = scale * sum over ranks of (a_r @ b_r.T), computed and exchanged by ONE kernel
+        (csrc/gemm_allreduce.cu). Returns this rank's view of the result inside its symmetric
+        buffer (bf16 [M, N] at out_off)."""
+        assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.shape[1] == b.shape[1]
+        a = a if a.stride(1) == 1 and a.stride(0) % 8 == 0 else a.contiguous()
+        b = b if b.stride(1) == 1 and b.stride(0) % 8 == 0 else b.contiguous()
+        m, k = a.shape
+        n = b.shape[0]
+        ldo = ldo or n
+        _lib.check(self._lib.tfop_gemm_allreduce_bf16_tn(
+            self._h, a.data_ptr(), b.data_ptr(), m, n, k, a.stride(0), b.stride(0), ldo,
+            float(scale), ws_off, out_off, max_ctas, _lib.stream_handle(stream)), "gemm_allreduce")
+        flat = self.view(out_off, (m - 1) * ldo + n, torch.bfloat16)
+        return torch.as_strided(flat, (m, n), (ldo, 1))
+
     def check_error(self) -> bool:
         flag = C.c_int(0)
         _lib.check(self._lib.tfop_comm_check_error(self._h, C.byref(flag)), "comm_check_error")
@@ -235,3 +258,19 @@ def all_reduce_emulated(comms: Sequence[SymmetricComm], n: int, *,
         _lib.dtype_tag(outs[0].dtype) if outs is not None else 0, _lib.dtype_tag(wire_dtype), n,
         sym_off, float(scale), algo, max_blocks, _lib.stream_handle(stream)),
         "allreduce_emulated")
+
+
+def gemm_all_reduce_emulated(comms: Sequence[SymmetricComm], a_list, b_list, *, ws_off: int,
+                             out_off: int, scale: float = 1.0, stream=None):
+    """All ranks of an emulated group in one cooperative launch (single-GPU tests)."""
+    lib = _lib.load()
+    world = len(comms)
+    m, k = a_list[0].shape
+    n = b_list[0].shape[0]
+    harr = (C.c_void_p * world)(*[c._h for c in comms])
+    aarr = (C.c_void_p * world)(*[t.data_ptr() for t in a_list])
+    barr = (C.c_void_p * world)(*[t.data_ptr() for t in b_list])
+    _lib.check(lib.tfop_gemm_allreduce_emulated(
+        harr, world, aarr, barr, m, n, k, a_list[0].stride(0), b_list[0].stride(0), n,
+        float(scale), ws_off, out_off, _lib.stream_handle(stream)), "gemm_allreduce_emulated")
+    return [c.view(out_off, m * n, torch.bfloat16).view(m, n) for c in comms]
