@@ -36,6 +36,7 @@ def main():
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
     cfg = getattr(BertConfig, args.model)()
+    cfg.tc_gemm = args.impl == "native"       # --impl nccl is the all-library baseline
     torch.manual_seed(1234)
     model = BertForPreTraining(cfg).to(dev).to(torch.bfloat16)
     nparam = sum((p.numel() + 7) // 8 * 8 for p in model.parameters())

@@ -288,3 +288,77 @@ def test_pytorchjob_env_rendezvous_gloo(cluster):
     logs = cli.get_logs("ptg", master=False)
     assert "rank 0 world 3 sum 6.0" in logs["ptg-master-0"]
     assert "rank 2 world 3 sum 6.0" in logs["ptg-worker-1"]
+
+
+# the reference's other example workloads, run as jobs ------------------------
+def _run_manifest(cluster, path, client_cls, overrides=None, timeout=150):
+    job = yaml.safe_load(open(os.path.join(REPO, path)))
+    if overrides:
+        overrides(job)
+    cli = client_cls(cluster=cluster)
+    cli.create(job)
+    name = job["metadata"]["name"]
+    cli.wait_for_job(name, polling_interval=0.2, timeout_seconds=timeout)
+    return cli, name
+
+
+def test_tf_smoke_job_chief_reaches_every_task(cluster):
+    cli, name = _run_manifest(cluster, "examples/tf_sample/tf_job_smoke.yaml", TFJobClient)
+    assert cli.is_job_succeeded(name)
+    log = cli.get_logs(name, master=True)[f"{name}-chief-0"]
+    for task in ("/job:chief/task:0", "/job:ps/task:1", "/job:worker/task:3"):
+        assert task + " ok" in log
+    assert "all tasks answered" in log
+
+
+def test_estimator_style_collective_allreduce_job(cluster):
+    cli, name = _run_manifest(cluster, "examples/distribution_strategy/estimator_api/distributed_tfjob.yaml",
+                              TFJobClient)
+    assert cli.is_job_succeeded(name)
+    logs = cli.get_logs(name, master=False)
+    assert len(logs) == 3 and all("eval loss" in t for t in logs.values())
+
+
+def test_keras_style_multi_worker_cnn_checkpoints_and_resumes(cluster, tmp_path):
+    def cpu(job):
+        ctr = job["spec"]["tfReplicaSpecs"]["Worker"]["template"]["spec"]["containers"][0]
+        ctr.pop("resources")
+        ctr["command"] = ctr["command"][:2] + ["--epochs", "1", "--steps-per-epoch", "30",
+                                               "--checkpoint_dir", str(tmp_path / "ckpt"),
+                                               "--saved_model_dir", str(tmp_path / "saved")]
+        ctr["env"] = [{"name": "CUDA_VISIBLE_DEVICES", "value": ""}]
+    cli, name = _run_manifest(cluster, "examples/distribution_strategy/keras_api/multi_worker_tfjob.yaml",
+                              TFJobClient, cpu)
+    assert cli.is_job_succeeded(name), cli.get_logs(name, master=False)
+    assert (tmp_path / "ckpt" / "ckpt.pt").exists() and (tmp_path / "saved" / "model.pt").exists()
+    cli.delete(name)
+    wait(lambda: not cluster.store.list("pods", "default", f"job-name={name}"))
+
+    def resume(job):
+        cpu(job)
+        ctr = job["spec"]["tfReplicaSpecs"]["Worker"]["template"]["spec"]["containers"][0]
+        ctr["command"][ctr["command"].index("--epochs") + 1] = "2"
+    cli, name = _run_manifest(cluster, "examples/distribution_strategy/keras_api/multi_worker_tfjob.yaml",
+                              TFJobClient, resume)
+    assert cli.is_job_succeeded(name)
+    assert "resumed from" in cli.get_logs(name, master=True)[f"{name}-worker-0"]
+
+
+def test_mnist_with_summaries_job(cluster, tmp_path):
+    def small(job):
+        ctr = job["spec"]["tfReplicaSpecs"]["Worker"]["template"]["spec"]["containers"][0]
+        ctr["command"] = ctr["command"][:2] + [f"--log_dir={tmp_path}", "--max_steps=120", "--learning_rate=0.01"]
+    cli, name = _run_manifest(cluster, "examples/mnist_with_summaries/tf_job_mnist.yaml", TFJobClient, small)
+    assert cli.is_job_succeeded(name)
+    events = [json.loads(l) for l in open(tmp_path / "test" / "events.jsonl")]
+    assert events[-1]["accuracy"] > 0.8 and "layer1/weights" in events[0]
+    assert any("trace_ms" in json.loads(l) for l in open(tmp_path / "train" / "events.jsonl"))
+
+
+def test_mxjob_kvstore_training(cluster):
+    from tf_operator_b200.sdk import MXJobClient
+    cli, name = _run_manifest(cluster, "examples/mxnet/mxjob_dist_v1.yaml", MXJobClient)
+    assert cli.is_job_succeeded(name)
+    log = cli.get_logs(name, master=False, replica_type="worker")[f"{name}-worker-0"]
+    assert "DMLC_ROLE=worker servers=1 workers=1 root=mxnet-job-scheduler-0:9091" in log and "final loss" in log
+    wait(lambda: set(phases(cluster, name)) == {f"{name}-worker-0"})     # cleanPodPolicy Running

@@ -66,6 +66,9 @@ class KindReconciler(JobController):
         job_key = c.key_of(job)
         specs = c.replica_specs(job, self.info)
         need = exp.satisfied_expectations(self.expectations, job_key, list(specs.keys()))
+        # elastic jobs are always synced, stale expectations or not (controller.go:336)
+        if (job.get("spec") or {}).get("enableDynamicWorker"):
+            need = True
         if not need or job.get("metadata", {}).get("deletionTimestamp"):
             log.info("reconcile cancelled: job %s does not need a reconcile or is being deleted "
                      "(sync=%s)", job_key, need)

@@ -28,6 +28,7 @@ class BertConfig:
     type_vocab: int = 2
     dropout: float = 0.0
     eps: float = 1e-12
+    tc_gemm: bool = True      # False: stock nn.Linear (cuBLAS) - the measured baseline graph
 
     @classmethod
     def large(cls):
@@ -42,15 +43,31 @@ class BertConfig:
         return cls(vocab_size=1024, hidden=128, layers=2, heads=2, intermediate=512, max_position=128)
 
 
+class _StockLinear(nn.Linear):
+    """nn.Linear + activation from torch ops (library GEMM): the baseline twin of TcLinear."""
+
+    def __init__(self, i, o, act: str = "none"):
+        super().__init__(i, o)
+        self.act = act
+
+    def forward(self, x):
+        y = F.linear(x, self.weight, self.bias)
+        return F.gelu(y) if self.act == "gelu" else y
+
+
+def _lin(c: "BertConfig", i, o, act="none"):
+    return TcLinear(i, o, act=act) if c.tc_gemm else _StockLinear(i, o, act)
+
+
 class BertLayer(nn.Module):
     def __init__(self, c: BertConfig):
         super().__init__()
         self.heads = c.heads
-        self.qkv = TcLinear(c.hidden, 3 * c.hidden)
-        self.proj = TcLinear(c.hidden, c.hidden)
+        self.qkv = _lin(c, c.hidden, 3 * c.hidden)
+        self.proj = _lin(c, c.hidden, c.hidden)
         self.ln1 = nn.LayerNorm(c.hidden, eps=c.eps)
-        self.fc1 = TcLinear(c.hidden, c.intermediate, act="gelu")
-        self.fc2 = TcLinear(c.intermediate, c.hidden)
+        self.fc1 = _lin(c, c.hidden, c.intermediate, "gelu")
+        self.fc2 = _lin(c, c.intermediate, c.hidden)
         self.ln2 = nn.LayerNorm(c.hidden, eps=c.eps)
 
     def forward(self, x, mask=None):
@@ -73,11 +90,11 @@ class BertForPreTraining(nn.Module):
         self.typ = nn.Embedding(c.type_vocab, c.hidden)
         self.ln = nn.LayerNorm(c.hidden, eps=c.eps)
         self.layers = nn.ModuleList(BertLayer(c) for _ in range(c.layers))
-        self.mlm_dense = TcLinear(c.hidden, c.hidden, act="gelu")
+        self.mlm_dense = _lin(c, c.hidden, c.hidden, "gelu")
         self.mlm_ln = nn.LayerNorm(c.hidden, eps=c.eps)
         self.mlm_bias = nn.Parameter(torch.zeros(c.vocab_size))
-        self.pooler = TcLinear(c.hidden, c.hidden)
-        self.nsp = TcLinear(c.hidden, 8)       # 2 classes, padded to 8 columns
+        self.pooler = _lin(c, c.hidden, c.hidden)
+        self.nsp = _lin(c, c.hidden, 8)       # 2 classes, padded to 8 columns
         self.apply(self._init)
 
     @staticmethod
@@ -101,7 +118,10 @@ class BertForPreTraining(nn.Module):
         from ..ops.gemm import linear
         x = self.encode(ids, token_type)
         h = self.mlm_ln(self.mlm_dense(x))
-        logits = linear(h, self.tok.weight, self.mlm_bias)      # tied decoder, tcgen05 GEMM
+        if self.cfg.tc_gemm:
+            logits = linear(h, self.tok.weight, self.mlm_bias)  # tied decoder, tcgen05 GEMM
+        else:
+            logits = F.linear(h, self.tok.weight, self.mlm_bias)
         mlm = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1),
                               ignore_index=-100)
         pooled = torch.tanh(self.pooler(x[:, 0]))

@@ -33,6 +33,16 @@ log = logging.getLogger("tf_operator_b200.operator")
 LEASE_DURATION, RENEW_DEADLINE, RETRY_PERIOD = 15.0, 5.0, 3.0   # server.go:54-59
 
 
+def _thread_dump() -> bytes:
+    import sys
+    import traceback
+    names = {t.ident: t.name for t in threading.enumerate()}
+    out = []
+    for ident, frame in sys._current_frames().items():
+        out.append(f"thread {names.get(ident, '?')} ({ident}):\n" + "".join(traceback.format_stack(frame)))
+    return "\n".join(out).encode()
+
+
 class EnabledSchemes(list):
     """Repeatable, case-insensitive --enable-scheme (register_controller.go:51-76)."""
 
@@ -115,6 +125,7 @@ class Manager:
         self._servers: List[ThreadingHTTPServer] = []
         self._last_seen: Dict[tuple, dict] = {}
         self._created_at: Dict[str, float] = {}
+        self._last_ads: Dict[str, object] = {}
         self.started = False
 
     # ------------------------------------------------------------------ events
@@ -129,14 +140,26 @@ class Manager:
             key = c.key_of(obj)
             if etype == "ADDED":
                 self._created_at.setdefault(f"{kind}:{key}", time.time())
+                self._last_ads[f"{kind}:{key}"] = c.run_policy(obj).get("activeDeadlineSeconds")
             if etype == "DELETED":
                 self._created_at.pop(f"{kind}:{key}", None)
+                self._last_ads.pop(f"{kind}:{key}", None)
                 for rt in c.replica_specs(obj, self.reconcilers[kind].info):
                     from ..engine import expectations as exp
                     e = self.reconcilers[kind].expectations
                     e.delete_expectations(exp.gen_expectation_pods_key(key, rt))
                     e.delete_expectations(exp.gen_expectation_services_key(key, rt))
                 return
+            if etype == "MODIFIED":
+                # re-arm the deadline timer when activeDeadlineSeconds is edited on a started job
+                # (updateTFJob, pkg/controller.v1/tensorflow/job.go:160-175)
+                ads = c.run_policy(obj).get("activeDeadlineSeconds")
+                start = (obj.get("status") or {}).get("startTime")
+                prev = self._last_ads.get(f"{kind}:{key}")
+                if ads is not None and start and prev is not None and prev != ads:
+                    remaining = float(ads) - (time.time() - c.parse_time(start))
+                    self.queues[kind].add_after(key, max(0.0, remaining))
+                self._last_ads[f"{kind}:{key}"] = ads
             if etype == "MODIFIED" and c.has_condition(c.status_of(obj), c.JOB_RUNNING):
                 t0 = self._created_at.pop(f"{kind}:{key}", None)
                 if t0 is not None:
@@ -294,7 +317,11 @@ class Manager:
         else:
             self.metrics.is_leader.set(1)
         self._serve(self.opt.metrics_bind_address, {
-            "/metrics": lambda: ("text/plain; version=0.0.4", self.metrics.render())})
+            "/metrics": lambda: ("text/plain; version=0.0.4", self.metrics.render()),
+            # net/http/pprof shares the legacy binary's metrics mux (cmd/tf-operator.v1/main.go:21,
+            # 39-50); the equivalent here is a goroutine-dump style listing of every thread's stack
+            "/debug/pprof/goroutine": lambda: ("text/plain", _thread_dump()),
+            "/debug/pprof/": lambda: ("text/plain", b"goroutine\n")})
         self._serve(self.opt.health_probe_bind_address, {
             "/healthz": lambda: ("text/plain", b"ok"), "/readyz": lambda: ("text/plain", b"ok")})
         self.started = True
