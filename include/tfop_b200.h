@@ -173,6 +173,11 @@ int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_ids_i64,
 int tfop_hist_build(const void* bins_u8, const float* grad, const float* hess,
                     const int* row_idx, size_t n_rows, int F, float* out, cudaStream_t stream);
 
+/* bf16 transpose out[C,R] = in[R,C]^T (csrc/transpose.cu); feeds the K-major operands of the
+ * weight-gradient GEMM. No reference counterpart. */
+int tfop_transpose_bf16(const void* in, void* out, int R, int C, int ld_in, int ld_out,
+                        cudaStream_t stream);
+
 /* ---- K7: tcgen05 / TMEM / TMA bf16 GEMM (csrc/gemm_tcgen05.cu) -----------
  * C[M,N] = epi(A[M,K] * B[N,K]^T + bias); the dense layers of
  * examples/v1/dist-mnist/dist_mnist.py:188-192. epilogue: 0 none, 1 bias,
@@ -192,6 +197,11 @@ int tfop_gemm_allreduce_set_timeout(long long cycles);
 int tfop_gemm_allreduce_bf16_tn(tfop_comm* c, const void* A, const void* B, int M, int N, int K,
                                 int lda, int ldb, int ldo, float scale, size_t ws_off,
                                 size_t out_off, int max_ctas, cudaStream_t stream);
+/* NVLS flavour: out region in the multicast-bound buffer, partials stay local, the NVSwitch
+ * reduces and broadcasts. ws_off: (tiles_per_owner + 2) * 4 zeroed bytes in the IPC buffer. */
+int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const void* B, int M, int N,
+                                     int K, int lda, int ldb, int ldo, float scale, size_t ws_off,
+                                     size_t out_off, int max_ctas, cudaStream_t stream);
 int tfop_gemm_allreduce_emulated(tfop_comm** comms, int world, const void* const* As,
                                  const void* const* Bs, int M, int N, int K, int lda, int ldb,
                                  int ldo, float scale, size_t ws_off, size_t out_off,

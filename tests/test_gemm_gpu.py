@@ -112,3 +112,12 @@ def test_fused_gemm_allreduce_emulated(gemm_ok):
     except subprocess.TimeoutExpired:
         pytest.fail("fused GEMM+all-reduce probe timed out")
     assert res.returncode == 0, f"{res.stdout}\n{res.stderr[-3000:]}"
+
+
+@pytest.mark.parametrize("r,c", [(64, 64), (8192, 1024), (1000, 77), (30528, 100), (5, 3)])
+def test_transpose_bf16(r, c):
+    from tf_operator_b200.ops.gemm import transpose
+    x = torch.randn(r, c, device="cuda").bfloat16()
+    assert torch.equal(transpose(x), x.t().contiguous())
+    xs = torch.randn(r, c + 8, device="cuda").bfloat16()[:, :c]     # strided rows
+    assert torch.equal(transpose(xs), xs.t().contiguous())

@@ -58,6 +58,8 @@ struct GarArgs {
     int tiles_per_owner;
     float scale;
     long long timeout;
+    char* nv_uc;                    // NVLS mode: local / multicast view of the bound buffer
+    char* nv_mc;
 };
 
 struct GarEmu {
@@ -74,7 +76,22 @@ __device__ __forceinline__ size_t slots_bytes(int world, int tpo) {
     return (size_t)world * tpo * kTileElems * 2;
 }
 __device__ __forceinline__ uint32_t* arrived_ptr(char* base, const GarArgs& a) {
-    return (uint32_t*)(base + a.ws_off + slots_bytes(a.world, a.tiles_per_owner));
+    return (uint32_t*)(base + a.ws_off + (a.nv_mc ? 0 : slots_bytes(a.world, a.tiles_per_owner)));
+}
+// 16 bytes of bf16 summed over every rank's copy inside the NVSwitch / stored to every copy
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16x8(const void* mc) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(mc)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void mm_st_16(void* mc, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc),
+                 "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                 "f"(__uint_as_float(v.w))
+                 : "memory");
 }
 __device__ __forceinline__ bool spin_until(const uint32_t* p, uint32_t target, uint32_t* err,
                                            long long timeout) {
@@ -88,6 +105,7 @@ __device__ __forceinline__ bool spin_until(const uint32_t* p, uint32_t target, u
     return true;
 }
 
+template <bool NVLS>
 __device__ void gemm_allreduce_body(const CUtensorMap& map_a, const CUtensorMap& map_b,
                                     const GarArgs& a) {
     using cfg = Cfg<BN>;
@@ -206,9 +224,21 @@ __device__ void gemm_allreduce_body(const CUtensorMap& map_a, const CUtensorMap&
             const int owner = t % W;
             const int slot = t / W;
             // partial tile of THIS rank inside the owner's HBM: [src rank][slot][128][256] bf16
-            __nv_bfloat16* dst = (__nv_bfloat16*)(a.data[owner] + a.ws_off) +
-                                 ((size_t)a.rank * a.tiles_per_owner + slot) * kTileElems +
-                                 (size_t)(ew * 32 + lane) * BN;
+            __nv_bfloat16* dst;
+            uint32_t row_bytes = BN * 2;
+            if (NVLS) {
+                // NVLS mode: the partial stays LOCAL, written at its final place in the
+                // multicast-bound output region; the switch sums the ranks' copies later
+                const int gr = (t / n_blocks) * BLOCK_M + ew * 32 + lane;
+                const int gc = (t % n_blocks) * BN;
+                dst = (__nv_bfloat16*)(a.nv_uc + a.out_off) + (size_t)gr * a.ldo + gc;
+                const int cols = min(BN, a.N - gc);
+                row_bytes = gr < a.M ? (uint32_t)cols * 2 : 0;
+            } else {
+                dst = (__nv_bfloat16*)(a.data[owner] + a.ws_off) +
+                      ((size_t)a.rank * a.tiles_per_owner + slot) * kTileElems +
+                      (size_t)(ew * 32 + lane) * BN;
+            }
             uint8_t* my_row = smem_stg + (size_t)(ew * 32 + lane) * kStgPitch;
             mbar_wait(&tmem_full[acc], acc_phase);
             tcgen05_fence_after();
@@ -233,9 +263,10 @@ __device__ void gemm_allreduce_body(const CUtensorMap& map_a, const CUtensorMap&
             if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             // one 512-byte bulk store per row, smem -> owner's HBM over NVLink (async proxy)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst),
-                         "r"(smem_u32(my_row)), "r"((uint32_t)(BN * 2))
-                         : "memory");
+            if (row_bytes)
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst),
+                             "r"(smem_u32(my_row)), "r"(row_bytes)
+                             : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
             asm volatile("fence.proxy.async;" ::: "memory");
@@ -263,9 +294,38 @@ __device__ void gemm_allreduce_body(const CUtensorMap& map_a, const CUtensorMap&
             const int n0 = (t % n_blocks) * BN;
             if (rt == 0) spin_until(my_arrived + j, gen * 4u * (uint32_t)W, a.err, a.timeout);
             reducer_bar();
+            if (NVLS) {
+                constexpr int UN = 4;
+                for (int v0 = rt; v0 < kTileElems / 8; v0 += kRedThreads * UN) {
+                    uint4 r[UN];
+                    size_t off[UN];
+                    bool ok[UN];
+#pragma unroll
+                    for (int u = 0; u < UN; ++u) {
+                        const int v = v0 + u * kRedThreads;
+                        const int gr = m0 + v / (BN / 8), gc = n0 + (v % (BN / 8)) * 8;
+                        ok[u] = gr < a.M && gc < a.N;
+                        off[u] = a.out_off + ((size_t)gr * a.ldo + gc) * 2;
+                        if (ok[u]) r[u] = mm_ld_reduce_bf16x8(a.nv_mc + off[u]);   // summed in the switch
+                    }
+#pragma unroll
+                    for (int u = 0; u < UN; ++u) {
+                        if (!ok[u]) continue;
+                        if (a.scale != 1.f) {
+                            float f[8];
+                            bf16x8_to_f32(*reinterpret_cast<bf16x8*>(&r[u]), f);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) f[i] *= a.scale;
+                            bf16x8 pk = f32_to_bf16x8(f);
+                            r[u] = *reinterpret_cast<uint4*>(&pk);
+                        }
+                        mm_st_16(a.nv_mc + off[u], r[u]);                          // to every rank
+                    }
+                }
+            }
             const __nv_bfloat16* slots = (const __nv_bfloat16*)(self + a.ws_off);
             constexpr int U = 4;   // vectors in flight per thread and source
-            for (int v0 = rt; v0 < kTileElems / 8; v0 += kRedThreads * U) {
+            for (int v0 = rt; !NVLS && v0 < kTileElems / 8; v0 += kRedThreads * U) {
                 float acc8[U][8];
 #pragma unroll
                 for (int u = 0; u < U; ++u)
@@ -335,7 +395,14 @@ __device__ void gemm_allreduce_body(const CUtensorMap& map_a, const CUtensorMap&
 __global__ void __launch_bounds__(kGarThreads, 1)
 gemm_allreduce_kernel(const __grid_constant__ CUtensorMap map_a,
                       const __grid_constant__ CUtensorMap map_b, const GarArgs a) {
-    gemm_allreduce_body(map_a, map_b, a);
+    gemm_allreduce_body<false>(map_a, map_b, a);
+}
+
+// NVLS flavour: partial tiles stay local, the NVSwitch reduces and broadcasts them
+__global__ void __launch_bounds__(kGarThreads, 1)
+gemm_allreduce_nvls_kernel(const __grid_constant__ CUtensorMap map_a,
+                           const __grid_constant__ CUtensorMap map_b, const GarArgs a) {
+    gemm_allreduce_body<true>(map_a, map_b, a);
 }
 
 struct EmuMaps {
@@ -346,7 +413,7 @@ struct EmuMaps {
 // all ranks on one GPU, one cooperative launch: blockIdx.y is the rank (world <= 4)
 __global__ void __launch_bounds__(kGarThreads, 1)
 gemm_allreduce_kernel_emu(const __grid_constant__ EmuMaps maps, const GarEmu e) {
-    gemm_allreduce_body(maps.a[blockIdx.y], maps.b[blockIdx.y], e.r[blockIdx.y]);
+    gemm_allreduce_body<false>(maps.a[blockIdx.y], maps.b[blockIdx.y], e.r[blockIdx.y]);
 }
 
 int tiles_per_owner(int M, int N, int W) {
@@ -425,6 +492,58 @@ TFOP_API int tfop_gemm_allreduce_bf16_tn(tfop_comm* c, const void* A, const void
     int grid = tiles < sms ? tiles : sms;
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
     gemm_allreduce_kernel<<<grid, kGarThreads, kGarSmemBytes, stream>>>(ma, mb, a);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// NVLS flavour of tfop_gemm_allreduce_bf16_tn: the result region is at out_off of the
+// communicator's multicast-bound buffer (tfop_nvls_bind), partial tiles never leave their GPU and
+// the NVSwitch does the summation (multimem.ld_reduce) and the broadcast (multimem.st).
+// ws_off: (tiles_per_owner + 2) * 4 bytes of zeroed counters in the IPC symmetric buffer.
+// N and ldo must be multiples of 8.
+TFOP_API int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const void* B, int M,
+                                              int N, int K, int lda, int ldb, int ldo, float scale,
+                                              size_t ws_off, size_t out_off, int max_ctas,
+                                              cudaStream_t stream) {
+    TFOP_REQUIRE(c != nullptr && !c->emulated, "needs a real communicator");
+    TFOP_REQUIRE(c->mc_ptr != nullptr, "NVLS is not set up on this communicator");
+    TFOP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "lda/ldb must be multiples of 8 elements (TMA)");
+    TFOP_REQUIRE(N % 8 == 0 && ldo % 8 == 0 && (out_off & 15) == 0,
+                 "NVLS mode needs N, ldo multiples of 8 and a 16-byte aligned out_off");
+    TFOP_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
+    const int tpo = tiles_per_owner(M, N, c->world);
+    TFOP_REQUIRE((ws_off & 15) == 0 && ws_off + ((size_t)tpo + 2) * 4 <= c->data_bytes,
+                 "counter workspace does not fit the symmetric buffer");
+    TFOP_REQUIRE(out_off + ((size_t)(M - 1) * ldo + N) * 2 <= c->mc_bytes,
+                 "output region does not fit the NVLS buffer");
+    GarArgs a;
+    memset(&a, 0, sizeof(a));
+    for (int p = 0; p < c->world; ++p) a.data[p] = (char*)c->data[p];
+    a.ws_off = ws_off;
+    a.out_off = out_off;
+    a.err = c->sig[c->rank] + TFOP_SIG_WORDS;
+    a.M = M; a.N = N; a.K = K; a.ldo = ldo;
+    a.rank = c->rank; a.world = c->world;
+    a.tiles_per_owner = tpo;
+    a.scale = scale;
+    a.timeout = g_spin_timeout;
+    a.nv_uc = (char*)c->mc_uc_ptr;
+    a.nv_mc = (char*)c->mc_ptr;
+    CUtensorMap ma, mb;
+    if (tfop_gemm_make_tensor_map(&ma, A, M, K, lda, BLOCK_M) != 0) return -1;
+    if (tfop_gemm_make_tensor_map(&mb, B, N, K, ldb, BN) != 0) return -1;
+    static bool attr = false;
+    if (!attr) {
+        TFOP_CUDA(cudaFuncSetAttribute(gemm_allreduce_nvls_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kGarSmemBytes));
+        attr = true;
+    }
+    int sms = 0;
+    if (tfop_gemm_num_sms(&sms) != 0) return -1;
+    const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
+    int grid = tiles < sms ? tiles : sms;
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    gemm_allreduce_nvls_kernel<<<grid, kGarThreads, kGarSmemBytes, stream>>>(ma, mb, a);
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }

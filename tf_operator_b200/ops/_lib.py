@@ -81,9 +81,13 @@ _SIGS = {
     "tfop_gemm_allreduce_bf16_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                             c_int, c_int, c_float, c_size_t, c_size_t, c_int,
                                             c_void_p]),
+    "tfop_gemm_allreduce_nvls_bf16_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                                 c_int, c_int, c_int, c_float, c_size_t, c_size_t,
+                                                 c_int, c_void_p]),
     "tfop_gemm_allreduce_emulated": (c_int, [C.POINTER(c_void_p), c_int, C.POINTER(c_void_p),
                                              C.POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int,
                                              c_int, c_float, c_size_t, c_size_t, c_void_p]),
+    "tfop_transpose_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
                                      c_int, c_float, c_float, c_float, c_int, c_void_p]),

@@ -47,6 +47,17 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor | None = None,
     return out
 
 
+def transpose(x: torch.Tensor) -> torch.Tensor:
+    """x[R, C] -> contiguous [C, R]; CUDA bf16 uses csrc/transpose.cu."""
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1):
+        return x.t().contiguous()
+    r, c = x.shape
+    out = torch.empty((c, r), dtype=x.dtype, device=x.device)
+    _lib.check(_lib.load().tfop_transpose_bf16(x.data_ptr(), out.data_ptr(), r, c, x.stride(0), r,
+                                               _lib.stream_handle()), "transpose_bf16")
+    return out
+
+
 class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, act):
@@ -78,10 +89,10 @@ class _LinearFn(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             # dX[M,K] = dY[M,N] @ W[N,K]  ==  TN(dY, W^T[K,N])
-            dx = gemm_tn(dy2, w.t().contiguous()).view(ctx.xshape)
+            dx = gemm_tn(dy2, transpose(w)).view(ctx.xshape)
         if ctx.needs_input_grad[1]:
             # dW[N,K] = dY^T[N,M] @ X[M,K]  ==  TN(dY^T[N,M], X^T[K,M])
-            dw = gemm_tn(dy2.t().contiguous(), x2.t().contiguous())
+            dw = gemm_tn(transpose(dy2), transpose(x2))
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.sum(0)
         return dx, dw, db, None

@@ -229,6 +229,22 @@ class SymmetricComm:
         flat = self.view(out_off, (m - 1) * ldo + n, torch.bfloat16)
         return torch.as_strided(flat, (m, n), (ldo, 1))
 
+    def gemm_all_reduce_nvls(self, a: torch.Tensor, b: torch.Tensor, *, ws_off: int, out_off: int = 0,
+                             ldo: Optional[int] = None, scale: float = 1.0, max_ctas: int = 0,
+                             stream=None) -> torch.Tensor:
+        """Fused GEMM + in-switch all-reduce; the result is this rank's view of the NVLS buffer."""
+        a = a if a.stride(1) == 1 and a.stride(0) % 8 == 0 else a.contiguous()
+        b = b if b.stride(1) == 1 and b.stride(0) % 8 == 0 else b.contiguous()
+        m, k = a.shape
+        n = b.shape[0]
+        ldo = ldo or n
+        _lib.check(self._lib.tfop_gemm_allreduce_nvls_bf16_tn(
+            self._h, a.data_ptr(), b.data_ptr(), m, n, k, a.stride(0), b.stride(0), ldo,
+            float(scale), ws_off, out_off, max_ctas, _lib.stream_handle(stream)),
+            "gemm_allreduce_nvls")
+        flat = self.nvls_view((m - 1) * ldo + n, torch.bfloat16, out_off)
+        return torch.as_strided(flat, (m, n), (ldo, 1))
+
     def check_error(self) -> bool:
         flag = C.c_int(0)
         _lib.check(self._lib.tfop_comm_check_error(self._h, C.byref(flag)), "comm_check_error")
