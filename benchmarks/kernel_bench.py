@@ -50,12 +50,19 @@ def timed(fn, iters=10, warm=5):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
+    ap.add_argument("--only", default="", help="gemm: just the GEMM table (plus the BERT-large shapes)")
     args = ap.parse_args()
     hbm, tf, src = peaks()
     res = {"peaks": {"hbm_gbs": hbm, "bf16_tflops": tf, "source": src}, "gemm": [], "bn": [], "optim": []}
     torch.manual_seed(0)
-    for (m, n, k) in [(8192, 8192, 8192), (4096, 4096, 4096), (16384, 4096, 1024), (16384, 1024, 4096),
-                      (8192, 1024, 1024), (4096, 1000, 2048)]:
+    shapes = [(8192, 8192, 8192), (4096, 4096, 4096), (16384, 4096, 1024), (16384, 1024, 4096),
+              (8192, 1024, 1024), (4096, 1000, 2048)]
+    if args.only == "gemm":
+        # BERT-large, 16 x 512 tokens: forward / dgrad / wgrad shapes of qkv, proj, fc1, fc2, decoder
+        shapes += [(8192, 3072, 1024), (8192, 4096, 1024), (8192, 1024, 4096), (8192, 1024, 3072),
+                   (3072, 1024, 8192), (1024, 1024, 8192), (4096, 1024, 8192), (1024, 4096, 8192),
+                   (8192, 30528, 1024), (8192, 1024, 30528), (30528, 1024, 8192)]
+    for (m, n, k) in shapes:
         a = torch.randn(m, k, device="cuda").bfloat16()
         b = torch.randn(n, k, device="cuda").bfloat16()
         row = {"m": m, "n": n, "k": k}
@@ -68,6 +75,12 @@ def main():
         row["frac_of_peak"] = round(best / tf, 3)
         row["vs_cublas"] = round(best / row["cublas_tflops"], 3)
         res["gemm"].append(row)
+        if args.only == "gemm":
+            print(row, flush=True)
+    if args.only == "gemm":
+        if args.out:
+            json.dump(res, open(args.out, "w"), indent=1)
+        return
     for shape in [(256, 64, 112, 112), (256, 256, 56, 56), (256, 512, 28, 28), (256, 1024, 14, 14), (256, 2048, 7, 7)]:
         n, c, h, w = shape
         x = torch.randn(shape, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)

@@ -185,6 +185,15 @@ int tfop_transpose_bf16(const void* in, void* out, int R, int C, int ld_in, int 
 int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias, int bias_dtype,
                       int M, int N, int K, int lda, int ldb, int ldc, int out_dtype,
                       int epilogue, int tile_n, cudaStream_t stream);
+/* General form: a_mn / b_mn = 1 means that operand is stored transposed ([K, M] resp. [K, N]
+ * row-major, "MN-major") and is fed to the tensor core as is - dgrad (x @ W, b_mn) and wgrad
+ * (dY^T @ X, a_mn + b_mn) of a linear layer need no transposed copies. */
+int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* bias, int bias_dtype,
+                   int M, int N, int K, int lda, int ldb, int ldc, int out_dtype, int epilogue,
+                   int tile_n, int a_mn, int b_mn, cudaStream_t stream);
+/* Test hook: 1 forces the per-thread direct C stores even where the TMA-store epilogue
+ * (32x128-byte swizzled boxes, used when ldc*elt and C are 16-byte multiples) applies. */
+int tfop_gemm_force_direct_store(int on);
 
 /* ---- fused GEMM -> reduce-scatter -> all-gather (csrc/gemm_allreduce.cu) ---------
  * Gradient GEMM + NCCL all-reduce of keras-API/multi_worker_strategy-with-keras.py:76-77,

@@ -50,6 +50,65 @@ def test_gemm_tn_matches_fp32(gemm_ok, m, n, k, tile_n):
     torch.testing.assert_close(c32, ref, rtol=1e-3, atol=1e-3 * (k ** 0.5))
 
 
+@pytest.mark.parametrize("m,n,k", [(128, 128, 64), (256, 512, 320), (1000, 520, 200), (72, 40, 24),
+                                   (1024, 1024, 8192), (3072, 1024, 2048)])
+@pytest.mark.parametrize("a_t,b_t", [(False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("tile_n", [128, 256])
+def test_gemm_mn_major_operands(gemm_ok, m, n, k, a_t, b_t, tile_n):
+    """Operands stored transposed are read MN-major by the tensor core (no transposed copy):
+    dgrad is (a_t=False, b_t=True), wgrad is (True, True)."""
+    from tf_operator_b200.ops.gemm import gemm
+    torch.manual_seed(m * 3 + n + k)
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b = torch.randn(n, k, device="cuda").bfloat16()
+    ref = a.float() @ b.float().t()
+    a_in = a.t().contiguous() if a_t else a
+    b_in = b.t().contiguous() if b_t else b
+    c = gemm(a_in, b_in, a_t=a_t, b_t=b_t, tile_n=tile_n)
+    torch.testing.assert_close(c.float(), ref, rtol=2e-2, atol=2e-2 * (k ** 0.5))
+    c32 = gemm(a_in, b_in, a_t=a_t, b_t=b_t, tile_n=tile_n, out_dtype=torch.float32)
+    torch.testing.assert_close(c32, ref, rtol=1e-3, atol=1e-3 * (k ** 0.5))
+
+
+@pytest.mark.parametrize("m,n,k", [(300, 1002, 128), (129, 2, 64), (4096, 1024, 1024)])
+def test_gemm_direct_store_path(gemm_ok, m, n, k):
+    """C layouts TMA cannot describe (row pitch not a 16-byte multiple) and the forced
+    direct-store hook must give the same numbers as the TMA-store epilogue."""
+    from tf_operator_b200.ops import _lib
+    from tf_operator_b200.ops.gemm import gemm_tn
+    torch.manual_seed(m + n)
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b = torch.randn(n, k, device="cuda").bfloat16()
+    bias = torch.randn(n, device="cuda")
+    ref = a.float() @ b.float().t() + bias
+    lib = _lib.load()
+    lib.tfop_gemm_force_direct_store(1)
+    try:
+        direct = gemm_tn(a, b, bias)
+        direct32 = gemm_tn(a, b, bias, out_dtype=torch.float32)
+    finally:
+        lib.tfop_gemm_force_direct_store(0)
+    auto = gemm_tn(a, b, bias)
+    torch.testing.assert_close(direct.float(), ref, rtol=2e-2, atol=2e-2 * (k ** 0.5))
+    torch.testing.assert_close(direct32, ref, rtol=1e-3, atol=1e-3 * (k ** 0.5))
+    assert torch.equal(auto, direct)
+
+
+def test_gemm_tma_store_into_strided_view(gemm_ok):
+    """out= a column slice of a wider buffer: the C tensor map carries the pitch, and nothing
+    outside the slice may be written."""
+    from tf_operator_b200.ops.gemm import gemm_tn
+    torch.manual_seed(11)
+    m, n, k = 520, 192, 320
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b = torch.randn(n, k, device="cuda").bfloat16()
+    wide = torch.full((m, 512), 7.0, device="cuda", dtype=torch.bfloat16)
+    gemm_tn(a, b, out=wide[:, 64:64 + n])
+    ref = a.float() @ b.float().t()
+    torch.testing.assert_close(wide[:, 64:64 + n].float(), ref, rtol=2e-2, atol=2e-2 * (k ** 0.5))
+    assert bool((wide[:, :64] == 7.0).all()) and bool((wide[:, 64 + n:] == 7.0).all())
+
+
 @pytest.mark.parametrize("epi", ["bias", "gelu", "relu", "gelu_tanh"])
 def test_gemm_epilogues(gemm_ok, epi):
     from tf_operator_b200.ops.gemm import gemm_tn

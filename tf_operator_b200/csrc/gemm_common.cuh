@@ -23,7 +23,12 @@ struct Cfg {
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
     static constexpr int kBarBytes = 256;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + align slack
+    // epilogue staging for TMA stores: per epilogue warp two 32-row x 128-byte swizzled boxes
+    static constexpr int kStoreBoxBytes = 32 * 128;
+    static constexpr int kStoreBytes = 4 * 2 * kStoreBoxBytes;
+    static constexpr int kBiasBytes = BN * 4;  // the tile's bias slice as fp32
+    static constexpr int kSmemBytes =
+        kStages * kStageBytes + kStoreBytes + kBarBytes + kBiasBytes + 1024;  // + align slack
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -61,6 +66,29 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+// TMA store of one swizzled shared-memory box into a 2D tensor; rows/columns outside the
+// tensor are clipped by the hardware, so M/N tails need no predicates.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0,
+                                             int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+        "r"(smem_u32(src)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_commit() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// barrier among the 128 epilogue threads only (id 0 is __syncthreads)
+__device__ __forceinline__ void epi_bar_sync() {
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -95,10 +123,28 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
     d |= (uint64_t)2 << 61;             // SWIZZLE_128B
     return d;
 }
+// MN-major operand tile (the operand is stored [K, MN] with MN contiguous) in SWIZZLE_128B
+// layout, as TMA delivers it in boxes of 64 K-rows x 64 MN-elements (128 bytes): k-rows 128
+// bytes apart, 8-row groups 1024 bytes apart (SBO), the next 64 MN-elements in the next box
+// 8192 bytes on (LBO). One UMMA_K=16 step advances the start address by 16 rows = 2048 bytes.
+constexpr int kMnBoxBytes = 64 * 128;
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(kMnBoxBytes >> 4) << 16;  // LBO
+    d |= (uint64_t)(1024 >> 4) << 32;         // SBO
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
 // kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major.
 __device__ __forceinline__ uint32_t make_idesc(int M, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) |
            ((uint32_t)(M >> 4) << 24);
+}
+// same with per-operand major-ness (bit 15: A is MN-major, bit 16: B is MN-major)
+__device__ __forceinline__ uint32_t make_idesc_major(int M, int N, int a_mn, int b_mn) {
+    return make_idesc(M, N) | ((uint32_t)(a_mn != 0) << 15) | ((uint32_t)(b_mn != 0) << 16);
 }
 __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t* r) {
     asm volatile(

@@ -23,18 +23,65 @@ using namespace tfop_gemm;
 
 enum { EPI_NONE = 0, EPI_BIAS = 1, EPI_BIAS_GELU = 2, EPI_BIAS_RELU = 3, EPI_BIAS_GELU_TANH = 4 };
 
+// bias + activation on 32 consecutive accumulator columns; sb = the fp32 bias of those columns
+// in shared memory (every lane reads the same address: one broadcast LDS.128 per 4 columns).
+// Loading bias from global memory per element put ~256 dependent L1 round trips into every
+// tile's epilogue and made the K=1024 forward GEMMs 3-4x slower than the bias-free ones.
+__device__ __forceinline__ void apply_epilogue(float* f, const float* sb, int epi) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(sb + j);
+        f[j] += b4.x;
+        f[j + 1] += b4.y;
+        f[j + 2] += b4.z;
+        f[j + 3] += b4.w;
+    }
+    if (epi == EPI_BIAS_GELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+    } else if (epi == EPI_BIAS_GELU_TANH) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = gelu_tanh(f[j]);
+    } else if (epi == EPI_BIAS_RELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+}
+
+// The 128 epilogue threads copy the tile's BN bias values (zero past N) into shared memory.
 template <int BN>
+__device__ __forceinline__ void stage_bias(float* sbias, const void* bias, int bias_dtype, int n0,
+                                           int N, int epi_tid) {
+    epi_bar_sync();  // the previous tile's readers are done
+    for (int i = epi_tid; i < BN; i += 128) {
+        const int col = n0 + i;
+        float v = 0.f;
+        if (col < N)
+            v = bias_dtype == TFOP_F32 ? __ldg((const float*)bias + col)
+                                       : __bfloat162float(((const __nv_bfloat16*)bias)[col]);
+        sbias[i] = v;
+    }
+    epi_bar_sync();
+}
+
+// kTmaStore: the epilogue converts into 128B-swizzled shared-memory boxes (32 rows x 128 bytes
+// per warp, double buffered) and one lane issues a TMA tensor store per box, so C is written in
+// whole 128-byte lines and the next tcgen05.ld is in flight while the current chunk is
+// converted. The direct-store path stays for C layouts TMA cannot describe (ldc*elt % 16 != 0).
+template <int BN, bool kTmaStore>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-               void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
-               int K, int ldc, int out_dtype, int epi) {
+               const __grid_constant__ CUtensorMap map_c, void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
+               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn) {
     using cfg = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     // 128B swizzle atoms need 1024-byte aligned tiles
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + cfg::kStages * cfg::kABytes;
-    uint64_t* bars = (uint64_t*)(smem + cfg::kStages * cfg::kStageBytes);
+    uint8_t* smem_store = smem + cfg::kStages * cfg::kStageBytes;
+    uint64_t* bars = (uint64_t*)(smem_store + cfg::kStoreBytes);
+    float* sbias = (float*)(smem_store + cfg::kStoreBytes + cfg::kBarBytes);
     uint64_t* full = bars;
     uint64_t* empty = bars + cfg::kStages;
     uint64_t* tmem_full = bars + 2 * cfg::kStages;
@@ -51,6 +98,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        if (kTmaStore) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < cfg::kStages; ++i) {
@@ -88,10 +136,25 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_expect_tx(&full[stage], cfg::kStageBytes);
-                    tma_load_2d(&map_a, &full[stage], smem_a + stage * cfg::kABytes, kb * BLOCK_K,
-                                m0);
-                    tma_load_2d(&map_b, &full[stage], smem_b + stage * cfg::kBBytes, kb * BLOCK_K,
-                                n0);
+                    uint8_t* sa = smem_a + stage * cfg::kABytes;
+                    uint8_t* sb = smem_b + stage * cfg::kBBytes;
+                    if (!a_mn) {
+                        tma_load_2d(&map_a, &full[stage], sa, kb * BLOCK_K, m0);
+                    } else {
+                        // A stored [K, M]: boxes of 64 k-rows x 64 m-elements
+#pragma unroll
+                        for (int j = 0; j < BLOCK_M / 64; ++j)
+                            tma_load_2d(&map_a, &full[stage], sa + j * kMnBoxBytes, m0 + 64 * j,
+                                        kb * BLOCK_K);
+                    }
+                    if (!b_mn) {
+                        tma_load_2d(&map_b, &full[stage], sb, kb * BLOCK_K, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(&map_b, &full[stage], sb + j * kMnBoxBytes, n0 + 64 * j,
+                                        kb * BLOCK_K);
+                    }
                     if (++stage == cfg::kStages) {
                         stage = 0;
                         phase ^= 1;
@@ -102,7 +165,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (elect_one()) {
-            const uint32_t idesc = make_idesc(BLOCK_M, BN);
+            const uint32_t idesc = make_idesc_major(BLOCK_M, BN, a_mn, b_mn);
+            // per-UMMA_K start-address step: 32 bytes along a K-major swizzle row, 16 k-rows
+            // (2048 bytes) of an MN-major box
+            const uint32_t a_step = a_mn ? 2048u : (uint32_t)(UMMA_K * 2);
+            const uint32_t b_step = b_mn ? 2048u : (uint32_t)(UMMA_K * 2);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -118,8 +185,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     const uint32_t b_addr = smem_u32(smem_b + stage * cfg::kBBytes);
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        const uint64_t adesc = make_smem_desc(a_addr + k * UMMA_K * 2);
-                        const uint64_t bdesc = make_smem_desc(b_addr + k * UMMA_K * 2);
+                        const uint64_t adesc = a_mn ? make_smem_desc_mn(a_addr + k * a_step)
+                                                    : make_smem_desc(a_addr + k * a_step);
+                        const uint64_t bdesc = b_mn ? make_smem_desc_mn(b_addr + k * b_step)
+                                                    : make_smem_desc(b_addr + k * b_step);
                         umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty[stage]);  // frees the smem slot when the MMAs retire
@@ -140,11 +209,111 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         const int ew = warp - kEpiWarp0;  // == warp % 4: TMEM lane quadrant
         int acc = 0;
         uint32_t acc_phase = 0;
+        if (kTmaStore) {
+            // chunk = 128 bytes of one output row: 64 bf16 or 32 fp32 columns
+            const int chunk_cols = out_dtype == TFOP_BF16 ? 64 : 32;
+            uint8_t* box0 = smem_store + ew * 2 * cfg::kStoreBoxBytes;
+            const uint32_t row_off = (uint32_t)lane * 128u;
+            const uint32_t sw = (uint32_t)(lane & 7);
+            int buf = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                int mb, nb;
+                tile_coords(t, m_blocks, n_blocks, mb, nb);
+                const int m0 = mb * BLOCK_M;
+                const int n0 = nb * BN;
+                if (epi != EPI_NONE)
+                    stage_bias<BN>(sbias, bias, bias_dtype, n0, N, ew * 32 + lane);
+                mbar_wait(&tmem_full[acc], acc_phase);
+                tcgen05_fence_after();
+                const uint32_t taddr =
+                    tmem_base + (uint32_t)(acc * BN) + ((uint32_t)(ew * 32) << 16);
+                uint32_t ra[32], rb[32];
+                tmem_ld_32x32b_x32(taddr, ra);
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 64) {
+                    // ---- columns c .. c+31 (in ra); prefetch c+32 .. c+63 into rb
+                    tmem_ld_wait();
+                    tmem_ld_32x32b_x32(taddr + (uint32_t)(c + 32), rb);
+                    uint8_t* box = box0 + buf * cfg::kStoreBoxBytes;
+                    // the store that last read this box must have drained it
+                    if (lane == 0) bulk_wait_read<1>();
+                    __syncwarp();
+                    float f[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(ra[j]);
+                    if (epi != EPI_NONE) apply_epilogue(f, sbias + c, epi);
+                    if (out_dtype == TFOP_BF16) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            bf16x8 pk = f32_to_bf16x8(f + 8 * j);
+                            *reinterpret_cast<uint4*>(box + row_off + (((uint32_t)j ^ sw) << 4)) =
+                                *reinterpret_cast<uint4*>(&pk);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(box + row_off + (((uint32_t)j ^ sw) << 4)) =
+                                make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                        fence_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (n0 + c < N && m0 + ew * 32 < M)
+                                tma_store_2d(&map_c, box, n0 + c, m0 + ew * 32);
+                            bulk_commit();
+                        }
+                        buf ^= 1;
+                        box = box0 + buf * cfg::kStoreBoxBytes;
+                        if (lane == 0) bulk_wait_read<1>();
+                        __syncwarp();
+                    }
+                    // ---- columns c+32 .. c+63 (in rb); prefetch the next chunk into ra
+                    tmem_ld_wait();
+                    if (c + 64 < BN) tmem_ld_32x32b_x32(taddr + (uint32_t)(c + 64), ra);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(rb[j]);
+                    if (epi != EPI_NONE) apply_epilogue(f, sbias + c + 32, epi);
+                    if (out_dtype == TFOP_BF16) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            bf16x8 pk = f32_to_bf16x8(f + 8 * j);
+                            *reinterpret_cast<uint4*>(box + row_off +
+                                                      (((uint32_t)(j + 4) ^ sw) << 4)) =
+                                *reinterpret_cast<uint4*>(&pk);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(box + row_off + (((uint32_t)j ^ sw) << 4)) =
+                                make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                    }
+                    fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        const int cc = out_dtype == TFOP_BF16 ? n0 + c : n0 + c + 32;
+                        if (cc < N && m0 + ew * 32 < M) tma_store_2d(&map_c, box, cc, m0 + ew * 32);
+                        bulk_commit();
+                    }
+                    buf ^= 1;
+                }
+                // every tcgen05.ld of this accumulator has completed: hand it back to the MMA warp
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                if (++acc == 2) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+            (void)chunk_cols;
+            if (lane == 0) bulk_wait_read<0>();  // smem must outlive the last store's read
+            __syncwarp();
+        } else {
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             int mb, nb;
             tile_coords(t, m_blocks, n_blocks, mb, nb);
             const int m0 = mb * BLOCK_M;
             const int n0 = nb * BN;
+            if (epi != EPI_NONE) stage_bias<BN>(sbias, bias, bias_dtype, n0, N, ew * 32 + lane);
             mbar_wait(&tmem_full[acc], acc_phase);
             tcgen05_fence_after();
             const int row = m0 + ew * 32 + lane;
@@ -159,25 +328,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     float f[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(r[j]);
-                    if (epi != EPI_NONE) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const int col = col0 + j;
-                            float bv = 0.f;
-                            if (col < N)
-                                bv = bias_dtype == TFOP_F32
-                                         ? ((const float*)bias)[col]
-                                         : __bfloat162float(((const __nv_bfloat16*)bias)[col]);
-                            float v = f[j] + bv;
-                            if (epi == EPI_BIAS_GELU)
-                                v = gelu_erf(v);
-                            else if (epi == EPI_BIAS_GELU_TANH)
-                                v = gelu_tanh(v);
-                            else if (epi == EPI_BIAS_RELU)
-                                v = fmaxf(v, 0.f);
-                            f[j] = v;
-                        }
-                    }
+                    if (epi != EPI_NONE) apply_epilogue(f, sbias + c, epi);
                     if (out_dtype == TFOP_BF16) {
                         __nv_bfloat16* crow = (__nv_bfloat16*)C + (size_t)row * ldc + col0;
                         if (col0 + 32 <= N && (((uintptr_t)crow) & 15) == 0) {
@@ -187,8 +338,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 *reinterpret_cast<uint4*>(crow + j) = *reinterpret_cast<uint4*>(&pk);
                             }
                         } else {
-                            for (int j = 0; j < 32 && col0 + j < N; ++j)
-                                crow[j] = __float2bfloat16_rn(f[j]);
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) crow[j] = __float2bfloat16_rn(f[j]);
                         }
                     } else {
                         float* crow = (float*)C + (size_t)row * ldc + col0;
@@ -198,7 +350,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 *reinterpret_cast<float4*>(crow + j) =
                                     make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
                         } else {
-                            for (int j = 0; j < 32 && col0 + j < N; ++j) crow[j] = f[j];
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (col0 + j < N) crow[j] = f[j];
                         }
                     }
                 }
@@ -210,6 +364,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 acc = 0;
                 acc_phase ^= 1;
             }
+        }
         }
     }
 
@@ -255,23 +410,47 @@ int make_map(CUtensorMap* map, const void* base, int rows, int K, int ld, int bo
     return 0;
 }
 
-int g_num_sms = 0;
+// C [M, N] row-major (ldc elements between rows) as a store target: boxes of 32 rows x 128
+// bytes (64 bf16 / 32 fp32 columns), 128B swizzle to match what the epilogue writes.
+int make_map_c(CUtensorMap* map, void* base, int M, int N, int ldc, int out_dtype) {
+    const int elt = out_dtype == TFOP_BF16 ? 2 : 4;
+    cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)M};
+    cuuint64_t strides[1] = {(cuuint64_t)ldc * elt};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / elt), 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(map,
+                          out_dtype == TFOP_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                          2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char msg[96];
+        snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled (C) failed with CUresult %d", (int)r);
+        tfop_set_error(__FILE__, __LINE__, msg);
+        return -1;
+    }
+    return 0;
+}
 
-template <int BN>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, void* C, const void* bias,
-           int bias_dtype, int M, int N, int K, int ldc, int out_dtype, int epi,
-           cudaStream_t stream) {
+int g_num_sms = 0;
+int g_force_direct_store = 0;
+
+template <int BN, bool kTmaStore>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, void* C,
+           const void* bias, int bias_dtype, int M, int N, int K, int ldc, int out_dtype, int epi,
+           int a_mn, int b_mn, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        TFOP_CUDA(cudaFuncSetAttribute(gemm_tn_kernel<BN>,
+        TFOP_CUDA(cudaFuncSetAttribute(gemm_tn_kernel<BN, kTmaStore>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg<BN>::kSmemBytes));
         attr_set = true;
     }
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-    gemm_tn_kernel<BN><<<grid, kNumThreads, Cfg<BN>::kSmemBytes, stream>>>(
-        ma, mb, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epi);
+    gemm_tn_kernel<BN, kTmaStore><<<grid, kNumThreads, Cfg<BN>::kSmemBytes, stream>>>(
+        ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epi, a_mn, b_mn);
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }
@@ -294,13 +473,19 @@ int tfop_gemm_num_sms(int* out) {
     return 0;
 }
 
-// C[M,N] = epi(A[M,K] * B[N,K]^T + bias[N]); A, B bf16 row-major with leading
-// dimensions lda/ldb (elements, multiples of 8; base pointers 16-byte aligned).
+// C[M,N] = epi(op(A) * op(B)^T + bias[N]), bf16 operands, fp32 accumulation in TMEM.
+//   a_mn = 0: A is [M, K] row-major (K-major), lda elements between rows
+//   a_mn = 1: A is [K, M] row-major (MN-major: the stored matrix is A^T), lda between K rows
+//   b_mn = 0: B is [N, K] row-major; b_mn = 1: B is [K, N] row-major
+// so (0,0) is F.linear(x, W); (0,1) is x @ W (dgrad straight from the stored weight); (1,1) is
+// A_stored^T @ B_stored (wgrad straight from dY and X) - no transposed copies anywhere.
+// Leading dimensions are multiples of 8 elements, base pointers 16-byte aligned.
 // out_dtype: TFOP_BF16 or TFOP_F32. epilogue: 0 none, 1 +bias, 2 +bias,GeLU(erf),
 // 3 +bias,ReLU, 4 +bias,GeLU(tanh). tile_n: 0 auto, 128 or 256.
-TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias,
-                               int bias_dtype, int M, int N, int K, int lda, int ldb, int ldc,
-                               int out_dtype, int epilogue, int tile_n, cudaStream_t stream) {
+TFOP_API int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* bias,
+                            int bias_dtype, int M, int N, int K, int lda, int ldb, int ldc,
+                            int out_dtype, int epilogue, int tile_n, int a_mn, int b_mn,
+                            cudaStream_t stream) {
     TFOP_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
     TFOP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "lda/ldb must be multiples of 8 elements (TMA)");
     TFOP_REQUIRE((((uintptr_t)A) & 15) == 0 && (((uintptr_t)B) & 15) == 0,
@@ -321,9 +506,34 @@ TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void
     }
     TFOP_REQUIRE(tile_n == 128 || tile_n == 256, "tile_n must be 0, 128 or 256");
     CUtensorMap ma, mb;
-    if (make_map(&ma, A, M, K, lda, BLOCK_M) != 0) return -1;
-    if (make_map(&mb, B, N, K, ldb, tile_n) != 0) return -1;
-    if (tile_n == 256)
-        return launch<256>(ma, mb, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, stream);
-    return launch<128>(ma, mb, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, stream);
+    // K-major: rows = MN extent, inner = K, box [BLOCK_M | tile_n rows, 64]
+    // MN-major: rows = K extent, inner = MN, box [64 k-rows, 64]
+    if (a_mn ? make_map(&ma, A, K, M, lda, BLOCK_K) : make_map(&ma, A, M, K, lda, BLOCK_M)) return -1;
+    if (b_mn ? make_map(&mb, B, K, N, ldb, BLOCK_K) : make_map(&mb, B, N, K, ldb, tile_n)) return -1;
+    // TMA can describe C when its row pitch and base are 16-byte multiples
+    const int elt = out_dtype == TFOP_BF16 ? 2 : 4;
+    const bool tma_store = !g_force_direct_store && ((size_t)ldc * elt) % 16 == 0 &&
+                           (((uintptr_t)C) & 15) == 0;
+    CUtensorMap mc = ma;
+    if (tma_store && make_map_c(&mc, C, M, N, ldc, out_dtype) != 0) return -1;
+#define TFOP_GEMM_LAUNCH(BN_, TMA_)                                                             \
+    launch<BN_, TMA_>(ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, a_mn, \
+                      b_mn, stream)
+    if (tile_n == 256) return tma_store ? TFOP_GEMM_LAUNCH(256, true) : TFOP_GEMM_LAUNCH(256, false);
+    return tma_store ? TFOP_GEMM_LAUNCH(128, true) : TFOP_GEMM_LAUNCH(128, false);
+#undef TFOP_GEMM_LAUNCH
+}
+
+// The "TN" special case kept as its own entry point: F.linear(x, W, b).
+TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias,
+                               int bias_dtype, int M, int N, int K, int lda, int ldb, int ldc,
+                               int out_dtype, int epilogue, int tile_n, cudaStream_t stream) {
+    return tfop_gemm_bf16(A, B, C, bias, bias_dtype, M, N, K, lda, ldb, ldc, out_dtype, epilogue,
+                          tile_n, 0, 0, stream);
+}
+
+// Test hook: 1 forces the direct (per-thread 16-byte) C stores even where TMA stores apply.
+TFOP_API int tfop_gemm_force_direct_store(int on) {
+    g_force_direct_store = on;
+    return 0;
 }

@@ -67,6 +67,9 @@ __global__ void __launch_bounds__(256) sgd_momentum_kernel(
     }
 }
 
+// Each thread owns 4 consecutive elements per trip: the fp32 streams move as one float4 per
+// thread (a warp covers 512 contiguous bytes per instruction), the bf16 streams as 8 bytes.
+// Two independent trips are in flight per iteration.
 template <bool GRAD_BF16>
 __global__ void __launch_bounds__(256) adamw_kernel(
     float* __restrict__ master, float* __restrict__ m1, float* __restrict__ m2,
@@ -76,36 +79,60 @@ __global__ void __launch_bounds__(256) adamw_kernel(
     const float b1 = hp[HP_B1], b2 = hp[HP_B2], eps = hp[HP_EPS], step = hp[HP_STEP];
     const float c1 = 1.f / (1.f - __powf(b1, step));
     const float c2 = 1.f / (1.f - __powf(b2, step));
-    const size_t nv = n / 8;
+    const float omb1 = 1.f - b1, omb2 = 1.f - b2;
+    const size_t nv = n / 4;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += stride) {
-        const size_t e0 = v * 8;
-        float g[8];
-        if (GRAD_BF16) {
-            uint4 raw = ld_stream_v4((const __nv_bfloat16*)grad + e0);
-            bf16x8_to_f32(*reinterpret_cast<bf16x8*>(&raw), g);
-        } else {
+    constexpr int U = 2;
+    for (size_t v0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nv; v0 += U * stride) {
+        float4 w[U], a[U], b[U], g[U];
+        bool ok[U];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) g[i] = ((const float*)grad)[e0 + i];
+        for (int u = 0; u < U; ++u) {
+            const size_t v = v0 + u * stride;
+            ok[u] = v < nv;
+            if (ok[u]) {
+                w[u] = __ldcs(reinterpret_cast<const float4*>(master) + v);
+                a[u] = __ldcs(reinterpret_cast<const float4*>(m1) + v);
+                b[u] = __ldcs(reinterpret_cast<const float4*>(m2) + v);
+                if (GRAD_BF16) {
+                    const uint2 raw = __ldcs(reinterpret_cast<const uint2*>(grad) + v);
+                    const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+                    const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+                    g[u] = make_float4(lo.x, lo.y, hi.x, hi.y);
+                } else {
+                    g[u] = __ldcs(reinterpret_cast<const float4*>(grad) + v);
+                }
+            }
         }
-        float w[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const size_t e = e0 + i;
-            const float gi = g[i] * gs;
-            const float a = b1 * m1[e] + (1.f - b1) * gi;
-            const float b = b2 * m2[e] + (1.f - b2) * gi * gi;
-            m1[e] = a;
-            m2[e] = b;
-            const float decay = e < n_decay ? wd : 0.f;
-            float wi = master[e];
-            wi -= lr * ((a * c1) / (sqrtf(b * c2) + eps) + decay * wi);
-            master[e] = wi;
-            w[i] = wi;
-        }
-        if (weights) {
-            bf16x8 pk = f32_to_bf16x8(w);
-            *reinterpret_cast<uint4*>(weights + e0) = *reinterpret_cast<uint4*>(&pk);
+        for (int u = 0; u < U; ++u) {
+            if (!ok[u]) continue;
+            const size_t v = v0 + u * stride;
+            const size_t e0 = v * 4;
+            float* wf = reinterpret_cast<float*>(&w[u]);
+            float* af = reinterpret_cast<float*>(&a[u]);
+            float* bf = reinterpret_cast<float*>(&b[u]);
+            const float* gf = reinterpret_cast<const float*>(&g[u]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float gi = gf[i] * gs;
+                af[i] = b1 * af[i] + omb1 * gi;
+                bf[i] = b2 * bf[i] + omb2 * gi * gi;
+                const float decay = (e0 + i) < n_decay ? wd : 0.f;
+                wf[i] -= lr * ((af[i] * c1) / (sqrtf(bf[i] * c2) + eps) + decay * wf[i]);
+            }
+            __stcs(reinterpret_cast<float4*>(master) + v, w[u]);
+            __stcs(reinterpret_cast<float4*>(m1) + v, a[u]);
+            __stcs(reinterpret_cast<float4*>(m2) + v, b[u]);
+            if (weights) {
+                __nv_bfloat162 lo = __floats2bfloat162_rn(wf[0], wf[1]);
+                __nv_bfloat162 hi = __floats2bfloat162_rn(wf[2], wf[3]);
+                uint2 pk;
+                pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                // the next forward reads these: keep them cacheable
+                *(reinterpret_cast<uint2*>(weights) + v) = pk;
+            }
         }
     }
 }
@@ -151,7 +178,7 @@ TFOP_API int tfop_adamw(float* master, float* m1, float* m2, const void* grad, i
     TFOP_REQUIRE(n % 8 == 0, "flat optimizer buffers must be padded to a multiple of 8 elements");
     TFOP_REQUIRE(grad_dtype == TFOP_BF16 || grad_dtype == TFOP_F32, "bad grad dtype");
     if (n == 0) return 0;
-    const int grid = grid_for(n / 8);
+    const int grid = grid_for(n / 8);  // two 4-element trips per thread and iteration
     if (grad_dtype == TFOP_BF16)
         adamw_kernel<true><<<grid, 256, 0, stream>>>(master, m1, m2, grad,
                                                      (__nv_bfloat16*)weights_bf16, n, n_decay,

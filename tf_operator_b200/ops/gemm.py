@@ -47,6 +47,46 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor | None = None,
     return out
 
 
+def _operand(t: torch.Tensor) -> torch.Tensor:
+    if t.stride(1) != 1 or t.stride(0) % 8 or t.data_ptr() % 16:
+        t = t.contiguous()
+        if t.shape[1] % 8:
+            t = F.pad(t, (0, 8 - t.shape[1] % 8))
+    return t
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor | None = None, epilogue: str = "none",
+         out_dtype=torch.bfloat16, tile_n: int = 0, a_t: bool = False, b_t: bool = False,
+         out: torch.Tensor | None = None, stream=None) -> torch.Tensor:
+    """General tcgen05 GEMM, C[M,N] = epi(op(a) @ op(b)^T + bias) with no transposed copies:
+
+      a_t=False: a is [M, K];  a_t=True: a is stored [K, M] (the tensor core reads it MN-major)
+      b_t=False: b is [N, K];  b_t=True: b is stored [K, N]
+
+    ``gemm(x, W)`` = F.linear; ``gemm(dy, W, b_t=True)`` = dy @ W (dgrad);
+    ``gemm(dy, x, a_t=True, b_t=True)`` = dy^T @ x (wgrad).
+    """
+    assert a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dim() == 2 and b.dim() == 2
+    m, k = (a.shape[1], a.shape[0]) if a_t else a.shape
+    n, kb = (b.shape[1], b.shape[0]) if b_t else b.shape
+    assert k == kb, f"contraction mismatch {k} vs {kb}"
+    # row pitch must be a 16-byte multiple; padded columns lie outside the TMA tensor extents
+    # (true M/N/K are passed), so they are never read
+    a, b = _operand(a), _operand(b)
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    epi = EPI[epilogue]
+    if bias is not None and epi == 0:
+        epi = 1
+    _lib.check(_lib.load().tfop_gemm_bf16(
+        a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias),
+        _lib.dtype_tag(bias.dtype) if bias is not None else 0, m, n, k, a.stride(0), b.stride(0),
+        out.stride(0), _lib.dtype_tag(out.dtype), epi, tile_n, int(a_t), int(b_t),
+        _lib.stream_handle(stream)), "gemm_bf16")
+    return out
+
+
 def transpose(x: torch.Tensor) -> torch.Tensor:
     """x[R, C] -> contiguous [C, R]; CUDA bf16 uses csrc/transpose.cu."""
     if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1):
@@ -80,19 +120,22 @@ class _LinearFn(torch.autograd.Function):
         x2, w, pre = ctx.saved_tensors
         dy2 = dy.reshape(-1, dy.shape[-1])
         if pre is not None:
-            with torch.enable_grad():
-                p = pre.detach().requires_grad_(True)
-                a = {"gelu": lambda t: F.gelu(t), "relu": F.relu,
-                     "gelu_tanh": lambda t: F.gelu(t, approximate="tanh")}[ctx.act](p)
-            dy2, = torch.autograd.grad(a, p, dy2)
+            # activation backward straight from the saved pre-activation (no forward re-run)
+            if ctx.act == "relu":
+                dy2 = torch.ops.aten.threshold_backward(dy2, pre, 0)
+            else:
+                dy2 = torch.ops.aten.gelu_backward(
+                    dy2, pre, approximate="tanh" if ctx.act == "gelu_tanh" else "none")
         dy2 = dy2.contiguous()
         dx = dw = db = None
+        mn_ok = dy2.shape[1] % 8 == 0 and w.shape[1] % 8 == 0 and x2.shape[1] % 8 == 0
         if ctx.needs_input_grad[0]:
-            # dX[M,K] = dY[M,N] @ W[N,K]  ==  TN(dY, W^T[K,N])
-            dx = gemm_tn(dy2, transpose(w)).view(ctx.xshape)
+            # dX[M,K] = dY[M,N] @ W[N,K]: W is the [contraction, K] matrix as stored -> MN-major B
+            dx = (gemm(dy2, w, b_t=True) if mn_ok else gemm_tn(dy2, transpose(w))).view(ctx.xshape)
         if ctx.needs_input_grad[1]:
-            # dW[N,K] = dY^T[N,M] @ X[M,K]  ==  TN(dY^T[N,M], X^T[K,M])
-            dw = gemm_tn(transpose(dy2), transpose(x2))
+            # dW[N,K] = dY^T @ X: both stored [tokens, *] -> both MN-major, contraction over rows
+            dw = (gemm(dy2, x2, a_t=True, b_t=True) if mn_ok
+                  else gemm_tn(transpose(dy2), transpose(x2)))
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.sum(0)
         return dx, dw, db, None
