@@ -41,5 +41,9 @@ def test_example_job_manifests_validate():
     from tf_operator_b200 import api
     for f in glob.glob(os.path.join(ROOT, "examples", "**", "*.yaml"), recursive=True):
         job = yaml.safe_load(open(f))
+        if job.get("kind") == "CustomResourceDefinition":     # examples/crd: legacy CRD manifests
+            assert job["spec"]["group"] in ("kubeflow.org", "scheduling.volcano.sh",
+                                            "scheduling.incubator.k8s.io"), f
+            continue
         api.set_defaults(job)
         api.validate(job)
