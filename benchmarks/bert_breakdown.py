@@ -45,12 +45,17 @@ def run(impl, model_name, B, S, top):
     shapes = []
     if impl == "native":
         from tf_operator_b200.ops import gemm as G
-        real = G.gemm_tn
+        real, real_g = G.gemm_tn, G.gemm
 
         def spy(a, b, *args, **kw):
             shapes.append((a.shape[0], b.shape[0], a.shape[1]))
             return real(a, b, *args, **kw)
-        G.gemm_tn = spy
+
+        def spy_g(a, b, *args, a_t=False, b_t=False, **kw):
+            m, k = (a.shape[1], a.shape[0]) if a_t else a.shape
+            shapes.append((m, b.shape[1] if b_t else b.shape[0], k))
+            return real_g(a, b, *args, a_t=a_t, b_t=b_t, **kw)
+        G.gemm_tn, G.gemm = spy, spy_g
     from torch.profiler import ProfilerActivity, profile
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         step()
@@ -63,7 +68,7 @@ def run(impl, model_name, B, S, top):
             a[1] += 1
     by_shape = {}
     if impl == "native":
-        G.gemm_tn = real
+        G.gemm_tn, G.gemm = real, real_g
         evs = sorted((e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA
                       and "gemm_tn_kernel" in e.name), key=lambda e: e.time_range.start)
         if len(evs) == len(shapes):

@@ -173,6 +173,28 @@ int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_ids_i64,
 int tfop_hist_build(const void* bins_u8, const float* grad, const float* hess,
                     const int* row_idx, size_t n_rows, int F, float* out, cudaStream_t stream);
 
+/* ---- K9: fused transformer-block elementwise ops (csrc/layernorm.cu) ------
+ * No reference counterpart (the reference ships no model code); the op list is BASELINE.json
+ * config 3. All tensors bf16, 16-byte aligned, H % 8 == 0.
+ * tfop_ln_fwd: y = LayerNorm(h + bias + res) * gamma + beta in one pass; s_out (the bf16 LN
+ *   input), mean, rstd (fp32 [rows]) are saved for backward; bias / res / s_out may be NULL.
+ * tfop_ln_bwd: one pass giving dx and, accumulated with fp32 RED into caller-zeroed [H]
+ *   buffers, dgamma, dbeta and dbias = colsum(dx) (the bias gradient of the producing linear
+ *   layer; may be NULL). H <= 1536 for both.
+ * tfop_bias_gelu_fwd: y = gelu_erf(h + bias).
+ * tfop_bias_act_bwd: act=1: dh = dy * gelu'(h + bias), dbias += colsum(dh); act=0: dbias +=
+ *   colsum(dy) only. */
+int tfop_ln_fwd(const void* h, const void* bias, const void* res, const void* gamma,
+                const void* beta, void* y, void* s_out, float* mean, float* rstd, int rows, int H,
+                float eps, cudaStream_t stream);
+int tfop_ln_bwd(const void* dy, const void* s, const float* mean, const float* rstd,
+                const void* gamma, void* dx, float* dgamma, float* dbeta, float* dbias, int rows,
+                int H, cudaStream_t stream);
+int tfop_bias_gelu_fwd(const void* h, const void* bias, void* y, int rows, int H,
+                       cudaStream_t stream);
+int tfop_bias_act_bwd(const void* dy, const void* h, const void* bias, void* dh, float* dbias,
+                      int rows, int H, int act, cudaStream_t stream);
+
 /* bf16 transpose out[C,R] = in[R,C]^T (csrc/transpose.cu); feeds the K-major operands of the
  * weight-gradient GEMM. No reference counterpart. */
 int tfop_transpose_bf16(const void* in, void* out, int R, int C, int ld_in, int ld_out,

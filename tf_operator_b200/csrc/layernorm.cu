@@ -1,0 +1,372 @@
+// K9: fused (bias + residual + LayerNorm) forward / backward and (bias + GeLU) forward /
+// backward for the transformer block (BASELINE.json config 3, BERT-large data-parallel).
+//
+// What is fused, and why: the GEMM output h of the attention projection / second MLP layer
+// goes through  s = h + bias + residual;  y = LN(s).  As separate torch ops that is an add
+// kernel, a LayerNorm kernel, and in backward a grad-input kernel, a gamma/beta kernel that ran
+// at 0.8 TB/s, a residual-grad add and a bias-grad column reduction - six passes over the
+// [tokens, hidden] tensor. Here forward is one pass and backward is one pass that also
+// produces the bias gradient (the column sum of dx) and dgamma / dbeta.
+//
+// Layout: one warp per row, the row lives in registers (hidden <= 1536, multiple of 8), each
+// lane owns 16-byte vectors lane, lane+32, ...; statistics are fp32 and computed on the
+// bf16-rounded sum so that forward and backward see the same s.
+//
+// Column reductions (dgamma, dbeta, dbias): each warp walks rows with a grid stride and keeps
+// per-column partials in registers, the block folds its warps through shared memory, then one
+// fp32 RED per column and block into pre-zeroed outputs.
+//
+// The reference has no model code; the op list is defined by BASELINE.json config 3.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kWarps = 8;  // per block
+constexpr float kInvSqrt2 = 0.70710678118654752f;
+constexpr float kInvSqrt2Pi = 0.3989422804014327f;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float* f) {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(p));
+    bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&raw), f);
+}
+__device__ __forceinline__ void load8_stream(const __nv_bfloat16* p, float* f) {
+    const uint4 raw = __ldcs(reinterpret_cast<const uint4*>(p));
+    bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(&raw), f);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* f) {
+    bf16x8 pk = f32_to_bf16x8(f);
+    *reinterpret_cast<uint4*>(p) = *reinterpret_cast<uint4*>(&pk);
+}
+__device__ __forceinline__ float round_bf16(float v) {
+    return __bfloat162float(__float2bfloat16_rn(v));
+}
+
+// y = LN(h + bias + res) * gamma + beta; s (the bf16 LN input), mean, rstd saved for backward.
+template <int NV>
+__global__ void __launch_bounds__(kWarps * 32)
+ln_fwd_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ bias,
+              const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ gamma,
+              const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+              __nv_bfloat16* __restrict__ s_out, float* __restrict__ mean_out,
+              float* __restrict__ rstd_out, int rows, int H, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nvec = H >> 3;
+    const size_t base = (size_t)row * H;
+    float v[NV][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int vec = lane + 32 * i;
+        if (vec < nvec) {
+            load8_stream(h + base + vec * 8, v[i]);
+            float t[8];
+            if (bias) {
+                load8(bias + vec * 8, t);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[i][j] += t[j];
+            }
+            if (res) {
+                load8_stream(res + base + vec * 8, t);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[i][j] += t[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                v[i][j] = round_bf16(v[i][j]);
+                sum += v[i][j];
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+        }
+    }
+    const float mean = warp_sum(sum) / (float)H;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        if (lane + 32 * i < nvec) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float d = v[i][j] - mean;
+                sq += d * d;
+            }
+        }
+    }
+    const float rstd = rsqrtf(warp_sum(sq) / (float)H + eps);
+    if (lane == 0) {
+        mean_out[row] = mean;
+        rstd_out[row] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int vec = lane + 32 * i;
+        if (vec < nvec) {
+            if (s_out) store8(s_out + base + vec * 8, v[i]);
+            float g[8], b[8], o[8];
+            load8(gamma + vec * 8, g);
+            load8(beta + vec * 8, b);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
+            store8(y + base + vec * 8, o);
+        }
+    }
+}
+
+// dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma,  xhat = (s - mean) * rstd
+// dgamma += dy * xhat, dbeta += dy, dbias += dx   (column sums, fp32 RED into zeroed buffers)
+template <int NV>
+__global__ void __launch_bounds__(kWarps * 32)
+ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ s,
+              const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+              const __nv_bfloat16* __restrict__ gamma, __nv_bfloat16* __restrict__ dx,
+              float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
+              int rows, int H) {
+    __shared__ float red[kWarps][32 * 8 + 8];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nvec = H >> 3;
+    const float inv_h = 1.f / (float)H;
+    float gam[NV][8], ag[NV][8], ab[NV][8], ax[NV][8];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int vec = lane + 32 * i;
+        if (vec < nvec) load8(gamma + vec * 8, gam[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ag[i][j] = ab[i][j] = ax[i][j] = 0.f;
+    }
+    for (int row = blockIdx.x * kWarps + warp; row < rows; row += gridDim.x * kWarps) {
+        const size_t base = (size_t)row * H;
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float d[NV][8], xh[NV][8];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vec = lane + 32 * i;
+            if (vec < nvec) {
+                load8_stream(dy + base + vec * 8, d[i]);
+                load8_stream(s + base + vec * 8, xh[i]);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    xh[i][j] = (xh[i][j] - mean) * rstd;
+                    ag[i][j] += d[i][j] * xh[i][j];
+                    ab[i][j] += d[i][j];
+                    d[i][j] *= gam[i][j];
+                    c1 += d[i][j];
+                    c2 += d[i][j] * xh[i][j];
+                }
+            }
+        }
+        c1 = warp_sum(c1) * inv_h;
+        c2 = warp_sum(c2) * inv_h;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vec = lane + 32 * i;
+            if (vec < nvec) {
+                float o[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    o[j] = round_bf16(rstd * (d[i][j] - c1 - xh[i][j] * c2));
+                    ax[i][j] += o[j];
+                }
+                store8(dx + base + vec * 8, o);
+            }
+        }
+    }
+    // fold the block's warps, one 256-column slab (i) and one quantity at a time
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            float* out = q == 0 ? dgamma : (q == 1 ? dbeta : dbias);
+            if (out == nullptr) continue;  // uniform
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                red[warp][lane * 8 + j] = q == 0 ? ag[i][j] : (q == 1 ? ab[i][j] : ax[i][j]);
+            __syncthreads();
+            const int col_in_slab = threadIdx.x;  // 256 threads <-> 256 columns
+            const int col = i * 256 + col_in_slab;
+            if (col < H) {
+                float t = 0.f;
+#pragma unroll
+                for (int w = 0; w < kWarps; ++w) t += red[w][col_in_slab];
+                atomicAdd(out + col, t);
+            }
+        }
+    }
+}
+
+// y = gelu(h + bias) (erf form); nothing saved - backward recomputes from h and bias.
+__global__ void __launch_bounds__(256)
+bias_gelu_fwd_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ bias,
+                     __nv_bfloat16* __restrict__ y, size_t nvec_total, int nvec_row) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec_total; v += stride) {
+        const int cv = (int)(v % (size_t)nvec_row);
+        float x[8], b[8], o[8];
+        load8_stream(h + v * 8, x);
+        load8(bias + cv * 8, b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float t = round_bf16(x[j] + b[j]);
+            o[j] = 0.5f * t * (1.f + erff(t * kInvSqrt2));
+        }
+        store8(y + v * 8, o);
+    }
+}
+
+// dh = dy * gelu'(h + bias), dbias += colsum(dh). act = 0: dh = dy (pure column sum, dh may be
+// null). Block = 32 column-vectors x 8 row lanes; each block walks a row band.
+__global__ void __launch_bounds__(256)
+bias_act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h,
+                    const __nv_bfloat16* __restrict__ bias, __nv_bfloat16* __restrict__ dh,
+                    float* __restrict__ dbias, int rows, int H, int act, int rows_per_block) {
+    __shared__ float red[8][32 * 8 + 8];
+    const int lx = threadIdx.x & 31;   // column vector within the 256-column slab
+    const int ly = threadIdx.x >> 5;   // row lane
+    const int vec = blockIdx.x * 32 + lx;
+    const int nvec = H >> 3;
+    const int r0 = blockIdx.y * rows_per_block;
+    const int r1 = min(rows, r0 + rows_per_block);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    if (vec < nvec) {
+        float b[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) b[j] = 0.f;
+        if (act && bias) load8(bias + vec * 8, b);
+        for (int r = r0 + ly; r < r1; r += 8) {
+            const size_t off = (size_t)r * H + vec * 8;
+            float d[8];
+            load8_stream(dy + off, d);
+            if (act) {
+                float x[8], o[8];
+                load8_stream(h + off, x);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float t = round_bf16(x[j] + b[j]);
+                    const float cdf = 0.5f * (1.f + erff(t * kInvSqrt2));
+                    const float pdf = kInvSqrt2Pi * __expf(-0.5f * t * t);
+                    o[j] = round_bf16(d[j] * (cdf + t * pdf));
+                    acc[j] += o[j];
+                }
+                store8(dh + off, o);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += d[j];
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[ly][lx * 8 + j] = acc[j];
+    __syncthreads();
+    const int col = blockIdx.x * 256 + threadIdx.x;
+    if (col < H) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+        atomicAdd(dbias + col, t);
+    }
+}
+
+template <int NV>
+int launch_fwd(const void* h, const void* bias, const void* res, const void* gamma,
+               const void* beta, void* y, void* s_out, float* mean, float* rstd, int rows, int H,
+               float eps, cudaStream_t stream) {
+    const int grid = (rows + kWarps - 1) / kWarps;
+    ln_fwd_kernel<NV><<<grid, kWarps * 32, 0, stream>>>(
+        (const __nv_bfloat16*)h, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)res,
+        (const __nv_bfloat16*)gamma, (const __nv_bfloat16*)beta, (__nv_bfloat16*)y,
+        (__nv_bfloat16*)s_out, mean, rstd, rows, H, eps);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int NV>
+int launch_bwd(const void* dy, const void* s, const float* mean, const float* rstd,
+               const void* gamma, void* dx, float* dgamma, float* dbeta, float* dbias, int rows,
+               int H, cudaStream_t stream) {
+    int grid = (rows + kWarps - 1) / kWarps;
+    if (grid > 148 * 2) grid = 148 * 2;
+    ln_bwd_kernel<NV><<<grid, kWarps * 32, 0, stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)s, mean, rstd, (const __nv_bfloat16*)gamma,
+        (__nv_bfloat16*)dx, dgamma, dbeta, dbias, rows, H);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+#define TFOP_LN_DISPATCH(FN, ...)                        \
+    switch ((H + 255) / 256) {                           \
+        case 1: return FN<1>(__VA_ARGS__);               \
+        case 2: return FN<2>(__VA_ARGS__);               \
+        case 3: return FN<3>(__VA_ARGS__);               \
+        case 4: return FN<4>(__VA_ARGS__);               \
+        case 5: return FN<5>(__VA_ARGS__);               \
+        default: return FN<6>(__VA_ARGS__);              \
+    }
+
+// y[rows,H] = LayerNorm(h + bias + res) * gamma + beta, all bf16; bias / res / s_out may be
+// null. mean / rstd: fp32 [rows]. H: multiple of 8, <= 1536 (the row and its three column
+// partials stay in registers: 227 at H = 1024, no spills); tensors 16-byte aligned.
+TFOP_API int tfop_ln_fwd(const void* h, const void* bias, const void* res, const void* gamma,
+                         const void* beta, void* y, void* s_out, float* mean, float* rstd,
+                         int rows, int H, float eps, cudaStream_t stream) {
+    TFOP_REQUIRE(rows > 0 && H > 0 && H % 8 == 0 && H <= 1536,
+                 "layernorm: hidden must be a multiple of 8 and <= 1536");
+    TFOP_LN_DISPATCH(launch_fwd, h, bias, res, gamma, beta, y, s_out, mean, rstd, rows, H, eps, stream);
+}
+
+// Backward of tfop_ln_fwd. dgamma / dbeta / dbias are fp32 [H] that the caller zeroed (they are
+// accumulated with RED); dbias may be null.
+TFOP_API int tfop_ln_bwd(const void* dy, const void* s, const float* mean, const float* rstd,
+                         const void* gamma, void* dx, float* dgamma, float* dbeta, float* dbias,
+                         int rows, int H, cudaStream_t stream) {
+    TFOP_REQUIRE(rows > 0 && H > 0 && H % 8 == 0 && H <= 1536,
+                 "layernorm: hidden must be a multiple of 8 and <= 1536");
+    TFOP_REQUIRE(dgamma != nullptr && dbeta != nullptr, "layernorm bwd needs dgamma and dbeta");
+    TFOP_LN_DISPATCH(launch_bwd, dy, s, mean, rstd, gamma, dx, dgamma, dbeta, dbias, rows, H, stream);
+}
+
+// y = gelu(h + bias), bf16 [rows, H], H % 8 == 0.
+TFOP_API int tfop_bias_gelu_fwd(const void* h, const void* bias, void* y, int rows, int H,
+                                cudaStream_t stream) {
+    TFOP_REQUIRE(rows > 0 && H > 0 && H % 8 == 0, "bias_gelu: H must be a multiple of 8");
+    const size_t nvec = (size_t)rows * (H / 8);
+    size_t blocks = (nvec + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    bias_gelu_fwd_kernel<<<(int)blocks, 256, 0, stream>>>(
+        (const __nv_bfloat16*)h, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, nvec, H / 8);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// act = 1: dh = dy * gelu'(h + bias) and dbias += colsum(dh); act = 0: dbias += colsum(dy)
+// (h, bias, dh unused). dbias: fp32 [H], zeroed by the caller.
+TFOP_API int tfop_bias_act_bwd(const void* dy, const void* h, const void* bias, void* dh,
+                               float* dbias, int rows, int H, int act, cudaStream_t stream) {
+    TFOP_REQUIRE(rows > 0 && H > 0 && H % 8 == 0, "bias_act_bwd: H must be a multiple of 8");
+    TFOP_REQUIRE(dbias != nullptr, "bias_act_bwd needs dbias");
+    TFOP_REQUIRE(act == 0 || (h != nullptr && dh != nullptr), "bias_act_bwd: act needs h and dh");
+    const int gx = (H / 8 + 31) / 32;
+    // enough row bands to fill the machine a few times over, at least 64 rows each
+    int gy = (148 * 8 + gx - 1) / gx;
+    int rpb = (rows + gy - 1) / gy;
+    if (rpb < 64) rpb = 64;
+    gy = (rows + rpb - 1) / rpb;
+    bias_act_bwd_kernel<<<dim3(gx, gy), 256, 0, stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const __nv_bfloat16*)bias,
+        (__nv_bfloat16*)dh, dbias, rows, H, act, rpb);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}

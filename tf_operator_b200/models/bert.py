@@ -14,7 +14,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from ..ops.gemm import TcLinear
+from ..ops.gemm import TcLinear, linear
+from ..ops.layernorm import add_bias_layernorm, bias_gelu
 
 
 @dataclass
@@ -63,6 +64,7 @@ class BertLayer(nn.Module):
     def __init__(self, c: BertConfig):
         super().__init__()
         self.heads = c.heads
+        self.fused = c.tc_gemm
         self.qkv = _lin(c, c.hidden, 3 * c.hidden)
         self.proj = _lin(c, c.hidden, c.hidden)
         self.ln1 = nn.LayerNorm(c.hidden, eps=c.eps)
@@ -72,11 +74,22 @@ class BertLayer(nn.Module):
 
     def forward(self, x, mask=None):
         b, s, h = x.shape
-        qkv = self.qkv(x).view(b, s, 3, self.heads, h // self.heads).permute(2, 0, 3, 1, 4)
-        a = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2], attn_mask=mask)
+        # unbind (not permute + index): its backward is one stack copy instead of three
+        # zero-filled [3, ...] tensors that are then added
+        q, k, v = self.qkv(x).view(b, s, 3, self.heads, h // self.heads).unbind(2)
+        a = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2),
+                                           attn_mask=mask)
         a = a.transpose(1, 2).reshape(b, s, h)
-        x = self.ln1(x + self.proj(a))
-        return self.ln2(x + self.fc2(self.fc1(x)))
+        if not self.fused:
+            x = self.ln1(x + self.proj(a))
+            return self.ln2(x + self.fc2(self.fc1(x)))
+        # tcgen05 GEMMs without epilogue; bias + residual + LayerNorm and bias + GeLU each run
+        # as one fused pass (ops/layernorm.py), whose backward also yields the bias gradients
+        x = add_bias_layernorm(linear(a, self.proj.weight), self.proj.bias, x,
+                               self.ln1.weight, self.ln1.bias, self.ln1.eps)
+        m = bias_gelu(linear(x, self.fc1.weight), self.fc1.bias)
+        return add_bias_layernorm(linear(m, self.fc2.weight), self.fc2.bias, x,
+                                  self.ln2.weight, self.ln2.bias, self.ln2.eps)
 
 
 class BertForPreTraining(nn.Module):
@@ -109,18 +122,23 @@ class BertForPreTraining(nn.Module):
         pos = torch.arange(s, device=ids.device)
         x = self.tok(ids) + self.pos(pos)[None] + self.typ(
             token_type if token_type is not None else torch.zeros_like(ids))
-        x = self.ln(x)
+        if self.cfg.tc_gemm:
+            x = add_bias_layernorm(x, None, None, self.ln.weight, self.ln.bias, self.ln.eps)
+        else:
+            x = self.ln(x)
         for l in self.layers:
             x = l(x)
         return x
 
     def forward(self, ids, mlm_labels, nsp_labels, token_type=None):
-        from ..ops.gemm import linear
         x = self.encode(ids, token_type)
-        h = self.mlm_ln(self.mlm_dense(x))
         if self.cfg.tc_gemm:
+            h = bias_gelu(linear(x, self.mlm_dense.weight), self.mlm_dense.bias)
+            h = add_bias_layernorm(h, None, None, self.mlm_ln.weight, self.mlm_ln.bias,
+                                   self.mlm_ln.eps)
             logits = linear(h, self.tok.weight, self.mlm_bias)  # tied decoder, tcgen05 GEMM
         else:
+            h = self.mlm_ln(self.mlm_dense(x))
             logits = F.linear(h, self.tok.weight, self.mlm_bias)
         mlm = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1),
                               ignore_index=-100)

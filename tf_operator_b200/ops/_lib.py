@@ -90,6 +90,13 @@ _SIGS = {
     "tfop_gemm_force_direct_store": (c_int, [c_int]),
     "tfop_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "tfop_ln_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                            c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "tfop_ln_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                            c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "tfop_bias_gelu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "tfop_bias_act_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                  c_int, c_void_p]),
     "tfop_transpose_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,

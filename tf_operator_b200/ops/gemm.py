@@ -137,7 +137,8 @@ class _LinearFn(torch.autograd.Function):
             dw = (gemm(dy2, x2, a_t=True, b_t=True) if mn_ok
                   else gemm_tn(transpose(dy2), transpose(x2)))
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dy2.sum(0)
+            from .layernorm import bias_grad
+            db = bias_grad(dy2)
         return dx, dw, db, None
 
 
