@@ -69,6 +69,12 @@ def main():
         for tn in (128, 256):
             us = timed(lambda: gemm_tn(a, b, tile_n=tn))
             row[f"tcgen05_tile{tn}_tflops"] = round(2 * m * n * k / us / 1e6, 1)
+        if args.only == "gemm":
+            from tf_operator_b200.ops import _lib
+            _lib.load().tfop_gemm_set_cluster_mode(0)
+            us = timed(lambda: gemm_tn(a, b, tile_n=256))
+            row["tile256_no_cluster_tflops"] = round(2 * m * n * k / us / 1e6, 1)
+            _lib.load().tfop_gemm_set_cluster_mode(-1)
         us = timed(lambda: torch.matmul(a, b.t()))
         row["cublas_tflops"] = round(2 * m * n * k / us / 1e6, 1)
         best = max(row["tcgen05_tile128_tflops"], row["tcgen05_tile256_tflops"])

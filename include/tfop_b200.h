@@ -213,6 +213,10 @@ int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void* bias, i
 int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* bias, int bias_dtype,
                    int M, int N, int K, int lda, int ldb, int ldc, int out_dtype, int epilogue,
                    int tile_n, int a_mn, int b_mn, cudaStream_t stream);
+/* -1 auto (default: pairs whenever there are >= 2 m-blocks), 0 never, 1 always: run the GEMM
+ * CTAs as cta_group::2 pairs (2-CTA clusters; one tcgen05.mma covers 256 rows, each SM stages
+ * only half of the B tile). */
+int tfop_gemm_set_cluster_mode(int mode);
 /* Test hook: 1 forces the per-thread direct C stores even where the TMA-store epilogue
  * (32x128-byte swizzled boxes, used when ldc*elt and C are 16-byte multiples) applies. */
 int tfop_gemm_force_direct_store(int on);

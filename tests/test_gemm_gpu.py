@@ -70,6 +70,52 @@ def test_gemm_mn_major_operands(gemm_ok, m, n, k, a_t, b_t, tile_n):
     torch.testing.assert_close(c32, ref, rtol=1e-3, atol=1e-3 * (k ** 0.5))
 
 
+CLUSTER_PROBE = r"""
+import torch
+from tf_operator_b200.ops import _lib
+from tf_operator_b200.ops.gemm import gemm
+lib = _lib.load()
+torch.manual_seed(5)
+cases = [(128, 256, 64), (384, 512, 320), (1000, 520, 200), (72, 40, 24), (4096, 4096, 1024),
+         (1024, 1024, 8192), (8192, 1024, 1024), (640, 1000, 4096)]
+for (m, n, k) in cases:
+    a = torch.randn(m, k, device='cuda').bfloat16()
+    b = torch.randn(n, k, device='cuda').bfloat16()
+    bias = torch.randn(n, device='cuda').bfloat16()
+    ref = a.float() @ b.float().t()
+    for a_t, b_t in ((False, False), (False, True), (True, True)):
+        ai = a.t().contiguous() if a_t else a
+        bi = b.t().contiguous() if b_t else b
+        for tn in (128, 256):
+            out = {}
+            for mode in (0, 1):
+                lib.tfop_gemm_set_cluster_mode(mode)
+                out[mode] = gemm(ai, bi, tile_n=tn, a_t=a_t, b_t=b_t)
+                outb = gemm(ai, bi, bias, tile_n=tn, a_t=a_t, b_t=b_t)
+                torch.cuda.synchronize()
+                err = (out[mode].float() - ref).abs().max().item()
+                assert err < 0.03 * k ** 0.5, (m, n, k, a_t, b_t, tn, mode, err)
+                errb = (outb.float() - ref - bias.float()).abs().max().item()
+                assert errb < 0.03 * k ** 0.5 + 0.05, (m, n, k, a_t, b_t, tn, mode, errb)
+            # same MMA order per tile: clustered and plain runs agree bit for bit
+            assert torch.equal(out[0], out[1]), (m, n, k, a_t, b_t, tn)
+lib.tfop_gemm_set_cluster_mode(-1)
+print('cluster ok')
+"""
+
+
+def test_gemm_cluster_multicast_matches_plain(gemm_ok):
+    """cta_group::2 CTA pairs (256-row MMAs, half of B per SM): numerics vs fp32 and bit-equality with
+    the unclustered kernel, over tails, odd m-block counts and all operand layouts. Runs in a
+    subprocess so a barrier mistake shows up as a timeout, not a hung test session."""
+    try:
+        res = subprocess.run([sys.executable, "-c", CLUSTER_PROBE], capture_output=True, text=True,
+                             timeout=240)
+    except subprocess.TimeoutExpired:
+        pytest.fail("clustered GEMM timed out (cross-CTA barrier deadlock)")
+    assert res.returncode == 0, res.stdout + res.stderr[-3000:]
+
+
 @pytest.mark.parametrize("m,n,k", [(300, 1002, 128), (129, 2, 64), (4096, 1024, 1024)])
 def test_gemm_direct_store_path(gemm_ok, m, n, k):
     """C layouts TMA cannot describe (row pitch not a 16-byte multiple) and the forced

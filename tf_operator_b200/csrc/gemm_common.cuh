@@ -15,11 +15,13 @@ constexpr int UMMA_K = 16;
 constexpr int kNumThreads = 256;
 constexpr int kEpiWarp0 = 4;
 
-template <int BN>
+// kPair = 2: the CTA is one half of a cta_group::2 pair and stages only BN/2 rows of B per
+// k-block (the tensor cores read the other half from the peer), which buys two more stages.
+template <int BN, int kPair = 1>
 struct Cfg {
-    static constexpr int kStages = BN == 256 ? 4 : 6;
+    static constexpr int kStages = kPair == 2 ? (BN == 256 ? 6 : 8) : (BN == 256 ? 4 : 6);
     static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
-    static constexpr int kBBytes = BN * BLOCK_K * 2;
+    static constexpr int kBBytes = (BN / kPair) * BLOCK_K * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
     static constexpr int kBarBytes = 256;
@@ -188,15 +190,71 @@ __device__ __forceinline__ float gelu_erf(float x) {
 // plain n-fastest order: L2 hit rate 74 %, every B tile re-read from HBM by each m-row; the
 // banded order shares each A tile ~9x and each B tile ~16x within a wave.
 constexpr int kGroupM = 16;
-__device__ __forceinline__ void tile_coords(int t, int m_blocks, int n_blocks, int& mb, int& nb) {
-    const int per_group = kGroupM * n_blocks;
+template <int GROUP>
+__device__ __forceinline__ void tile_coords_g(int t, int m_blocks, int n_blocks, int& mb, int& nb) {
+    const int per_group = GROUP * n_blocks;
     const int group = t / per_group;
-    const int first_m = group * kGroupM;
-    const int gm = min(kGroupM, m_blocks - first_m);
+    const int first_m = group * GROUP;
+    const int gm = min(GROUP, m_blocks - first_m);
     const int r = t - group * per_group;
     mb = first_m + r % gm;
     nb = r / gm;
 }
+__device__ __forceinline__ void tile_coords(int t, int m_blocks, int n_blocks, int& mb, int& nb) {
+    tile_coords_g<kGroupM>(t, m_blocks, n_blocks, mb, nb);
+}
 
+// ---- thread-block cluster helpers (2-CTA clusters sharing the B tile by TMA multicast) ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// ---- cta_group::2 (CTA pair) variants -----------------------------------------------------
+// Shared-window addresses carry the CTA's rank within the pair in bit 24: clearing it names
+// the same offset in the even ("leader") CTA.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+
+// TMA load issued by either CTA of a pair into its own shared memory; the bytes are counted on
+// the LEADER's barrier, which the (leader-only) MMA thread waits on.
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint64_t* bar, void* dst,
+                                                 int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+        : "memory");
+}
+// One 256 x N x 16 MMA executed by both SMs of the pair (each on its 128 rows of A / D and its
+// N/2 rows of B); issued by the leader CTA only.
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                               uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Completion of the pair's MMAs, delivered to the barrier at this offset in both CTAs.
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
+        " [%0], %1;" ::"r"(smem_u32(bar)),
+        "h"((uint16_t)3)
+        : "memory");
+}
+// Arrive on the leader CTA's barrier from either CTA of the pair.
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(
+                     smem_u32(bar) & kPeerBitMask)
+                 : "memory");
+}
 
 }  // namespace tfop_gemm

@@ -68,12 +68,22 @@ __device__ __forceinline__ void stage_bias(float* sbias, const void* bias, int b
 // per warp, double buffered) and one lane issues a TMA tensor store per box, so C is written in
 // whole 128-byte lines and the next tcgen05.ld is in flight while the current chunk is
 // converted. The direct-store path stays for C layouts TMA cannot describe (ldc*elt % 16 != 0).
-template <int BN, bool kTmaStore>
+//
+// kCluster = 2: CTAs run as cta_group::2 pairs on vertically adjacent tiles (same n-block). One
+// tcgen05.mma covers 256 x BN: each SM multiplies its own 128 rows of A with the whole B tile,
+// of which it stages only its BN/2 rows - the tensor cores fetch the other half from the peer.
+// Per k-block a CTA writes and reads 32 KB of shared memory instead of 48 KB (BN = 256), which
+// is what the single-CTA kernel is bound by (multicasting B alone changed nothing). Only the
+// even CTA issues MMAs; TMA loads of both CTAs count on its `full` barrier, its commits are
+// multicast to both CTAs' `empty` / `tmem_full` barriers, and both epilogues arrive on its
+// `tmem_empty`.
+template <int BN, bool kTmaStore, int kCluster>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_c, void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
                int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn) {
-    using cfg = Cfg<BN>;
+    using cfg = Cfg<BN, kCluster>;
+    constexpr bool kPair = kCluster == 2;
     extern __shared__ uint8_t smem_raw[];
     // 128B swizzle atoms need 1024-byte aligned tiles
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -92,8 +102,14 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int lane = threadIdx.x & 31;
     const int m_blocks = (M + BLOCK_M - 1) / BLOCK_M;
     const int n_blocks = (N + BN - 1) / BN;
-    const int num_tiles = m_blocks * n_blocks;
     const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+    // scheduling unit: one m-block, or a vertical pair of m-blocks per cluster
+    constexpr int kGroup = kCluster == 2 ? kGroupM / 2 : kGroupM;
+    const int crank = kCluster == 2 ? (int)cluster_ctarank() : 0;
+    const int m_units = (m_blocks + kCluster - 1) / kCluster;
+    const int num_tiles = m_units * n_blocks;
+    const int t_first = blockIdx.x / kCluster;
+    const int t_step = gridDim.x / kCluster;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -107,19 +123,29 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+            mbar_init(&tmem_empty[i], 4 * kCluster);  // one arrive per epilogue warp (of the pair)
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                         smem_u32(tmem_slot)),
-                     "r"((uint32_t)cfg::kTmemCols)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (kPair) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32(tmem_slot)),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32(tmem_slot)),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tcgen05_fence_before();
     __syncthreads();
+    // the peer's barriers must be initialised before anything of ours can arrive on them
+    if (kCluster == 2) cluster_sync_all();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -128,32 +154,55 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = t_first; t < num_tiles; t += t_step) {
                 int mb, nb;
-                tile_coords(t, m_blocks, n_blocks, mb, nb);
-                const int m0 = mb * BLOCK_M;
+                tile_coords_g<kGroup>(t, m_units, n_blocks, mb, nb);
+                const int m0 = (mb * kCluster + crank) * BLOCK_M;
                 const int n0 = nb * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
-                    mbar_expect_tx(&full[stage], cfg::kStageBytes);
                     uint8_t* sa = smem_a + stage * cfg::kABytes;
                     uint8_t* sb = smem_b + stage * cfg::kBBytes;
-                    if (!a_mn) {
-                        tma_load_2d(&map_a, &full[stage], sa, kb * BLOCK_K, m0);
-                    } else {
-                        // A stored [K, M]: boxes of 64 k-rows x 64 m-elements
+                    if (kPair) {
+                        // the leader's barrier counts the bytes of both CTAs
+                        if (crank == 0) mbar_expect_tx(&full[stage], 2 * cfg::kStageBytes);
+                        if (!a_mn) {
+                            tma_load_2d_pair(&map_a, &full[stage], sa, kb * BLOCK_K, m0);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < BLOCK_M / 64; ++j)
-                            tma_load_2d(&map_a, &full[stage], sa + j * kMnBoxBytes, m0 + 64 * j,
-                                        kb * BLOCK_K);
-                    }
-                    if (!b_mn) {
-                        tma_load_2d(&map_b, &full[stage], sb, kb * BLOCK_K, n0);
-                    } else {
+                            for (int j = 0; j < BLOCK_M / 64; ++j)
+                                tma_load_2d_pair(&map_a, &full[stage], sa + j * kMnBoxBytes,
+                                                 m0 + 64 * j, kb * BLOCK_K);
+                        }
+                        // this CTA's half of the B tile
+                        const int nh = n0 + crank * (BN / 2);
+                        if (!b_mn) {
+                            tma_load_2d_pair(&map_b, &full[stage], sb, kb * BLOCK_K, nh);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < BN / 64; ++j)
-                            tma_load_2d(&map_b, &full[stage], sb + j * kMnBoxBytes, n0 + 64 * j,
-                                        kb * BLOCK_K);
+                            for (int j = 0; j < BN / 128; ++j)
+                                tma_load_2d_pair(&map_b, &full[stage], sb + j * kMnBoxBytes,
+                                                 nh + 64 * j, kb * BLOCK_K);
+                        }
+                    } else {
+                        mbar_expect_tx(&full[stage], cfg::kStageBytes);
+                        if (!a_mn) {
+                            tma_load_2d(&map_a, &full[stage], sa, kb * BLOCK_K, m0);
+                        } else {
+                            // A stored [K, M]: boxes of 64 k-rows x 64 m-elements
+#pragma unroll
+                            for (int j = 0; j < BLOCK_M / 64; ++j)
+                                tma_load_2d(&map_a, &full[stage], sa + j * kMnBoxBytes,
+                                            m0 + 64 * j, kb * BLOCK_K);
+                        }
+                        if (!b_mn) {
+                            tma_load_2d(&map_b, &full[stage], sb, kb * BLOCK_K, n0);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < BN / 64; ++j)
+                                tma_load_2d(&map_b, &full[stage], sb + j * kMnBoxBytes,
+                                            n0 + 64 * j, kb * BLOCK_K);
+                        }
                     }
                     if (++stage == cfg::kStages) {
                         stage = 0;
@@ -163,9 +212,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (elect_one()) {
-            const uint32_t idesc = make_idesc_major(BLOCK_M, BN, a_mn, b_mn);
+        // ===================== MMA issuer (the even CTA of a pair) =====================
+        if ((!kPair || crank == 0) && elect_one()) {
+            const uint32_t idesc = make_idesc_major(BLOCK_M * kCluster, BN, a_mn, b_mn);
             // per-UMMA_K start-address step: 32 bytes along a K-major swizzle row, 16 k-rows
             // (2048 bytes) of an MN-major box
             const uint32_t a_step = a_mn ? 2048u : (uint32_t)(UMMA_K * 2);
@@ -174,7 +223,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = t_first; t < num_tiles; t += t_step) {
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 tcgen05_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
@@ -189,15 +238,26 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                                     : make_smem_desc(a_addr + k * a_step);
                         const uint64_t bdesc = b_mn ? make_smem_desc_mn(b_addr + k * b_step)
                                                     : make_smem_desc(b_addr + k * b_step);
-                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (kPair)
+                            umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        else
+                            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    umma_commit(&empty[stage]);  // frees the smem slot when the MMAs retire
+                    // frees the smem slot when the MMAs retire (in both CTAs of a pair)
+                    if (kPair)
+                        umma_commit_pair(&empty[stage]);
+                    else
+                        umma_commit(&empty[stage]);
                     if (++stage == cfg::kStages) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit(&tmem_full[acc]);  // accumulator ready for the epilogue
+                // accumulator ready for the epilogue (of both CTAs of a pair)
+                if (kPair)
+                    umma_commit_pair(&tmem_full[acc]);
+                else
+                    umma_commit(&tmem_full[acc]);
                 if (++acc == 2) {
                     acc = 0;
                     acc_phase ^= 1;
@@ -216,10 +276,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const uint32_t row_off = (uint32_t)lane * 128u;
             const uint32_t sw = (uint32_t)(lane & 7);
             int buf = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = t_first; t < num_tiles; t += t_step) {
                 int mb, nb;
-                tile_coords(t, m_blocks, n_blocks, mb, nb);
-                const int m0 = mb * BLOCK_M;
+                tile_coords_g<kGroup>(t, m_units, n_blocks, mb, nb);
+                const int m0 = (mb * kCluster + crank) * BLOCK_M;
                 const int n0 = nb * BN;
                 if (epi != EPI_NONE)
                     stage_bias<BN>(sbias, bias, bias_dtype, n0, N, ew * 32 + lane);
@@ -298,7 +358,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 // every tcgen05.ld of this accumulator has completed: hand it back to the MMA warp
                 tcgen05_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                if (lane == 0) {
+                    if (kPair)
+                        mbar_arrive_leader(&tmem_empty[acc]);
+                    else
+                        mbar_arrive(&tmem_empty[acc]);
+                }
                 if (++acc == 2) {
                     acc = 0;
                     acc_phase ^= 1;
@@ -308,10 +373,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             if (lane == 0) bulk_wait_read<0>();  // smem must outlive the last store's read
             __syncwarp();
         } else {
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        for (int t = t_first; t < num_tiles; t += t_step) {
             int mb, nb;
-            tile_coords(t, m_blocks, n_blocks, mb, nb);
-            const int m0 = mb * BLOCK_M;
+            tile_coords_g<kGroup>(t, m_units, n_blocks, mb, nb);
+            const int m0 = (mb * kCluster + crank) * BLOCK_M;
             const int n0 = nb * BN;
             if (epi != EPI_NONE) stage_bias<BN>(sbias, bias, bias_dtype, n0, N, ew * 32 + lane);
             mbar_wait(&tmem_full[acc], acc_phase);
@@ -359,7 +424,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
             tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            if (lane == 0) {
+                    if (kPair)
+                        mbar_arrive_leader(&tmem_empty[acc]);
+                    else
+                        mbar_arrive(&tmem_empty[acc]);
+                }
             if (++acc == 2) {
                 acc = 0;
                 acc_phase ^= 1;
@@ -370,11 +440,19 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 
     tcgen05_fence_before();
     __syncthreads();
+    // the leader's commits still land on this CTA's barriers and its MMAs read this CTA's
+    // shared memory: leave together
+    if (kCluster == 2) cluster_sync_all();
     if (warp == 2) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                     "r"((uint32_t)cfg::kTmemCols)
-                     : "memory");
+        if (kPair)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
     }
 }
 
@@ -436,22 +514,57 @@ int make_map_c(CUtensorMap* map, void* base, int M, int N, int ldc, int out_dtyp
 int g_num_sms = 0;
 int g_force_direct_store = 0;
 
-template <int BN, bool kTmaStore>
+int g_cluster_mode = -1;  // -1 auto, 0 off, 1 force clusters of two
+
+template <int BN, bool kTmaStore, int kCluster>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, void* C,
            const void* bias, int bias_dtype, int M, int N, int K, int ldc, int out_dtype, int epi,
            int a_mn, int b_mn, cudaStream_t stream) {
     static bool attr_set = false;
+    static int max_ctas = 0;
+    auto kern = gemm_tn_kernel<BN, kTmaStore, kCluster>;
     if (!attr_set) {
-        TFOP_CUDA(cudaFuncSetAttribute(gemm_tn_kernel<BN, kTmaStore>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg<BN>::kSmemBytes));
+        TFOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<BN, kCluster>::kSmemBytes));
+        max_ctas = g_num_sms;
+        if (kCluster == 2) {
+            // how many 2-CTA clusters can be resident at once (GPCs with an odd SM count lose one)
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(g_num_sms / 2 * 2);
+            q.blockDim = dim3(kNumThreads);
+            q.dynamicSmemBytes = Cfg<BN, kCluster>::kSmemBytes;
+            cudaLaunchAttribute qa[1];
+            qa[0].id = cudaLaunchAttributeClusterDimension;
+            qa[0].val.clusterDim.x = 2;
+            qa[0].val.clusterDim.y = 1;
+            qa[0].val.clusterDim.z = 1;
+            q.attrs = qa;
+            q.numAttrs = 1;
+            int n = 0;
+            TFOP_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &q));
+            TFOP_REQUIRE(n > 0, "no 2-CTA cluster of the GEMM kernel fits on this device");
+            max_ctas = 2 * n;
+        }
         attr_set = true;
     }
-    const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
-    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-    gemm_tn_kernel<BN, kTmaStore><<<grid, kNumThreads, Cfg<BN>::kSmemBytes, stream>>>(
-        ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epi, a_mn, b_mn);
-    TFOP_CUDA(cudaGetLastError());
+    const int m_units = ((M + BLOCK_M - 1) / BLOCK_M + kCluster - 1) / kCluster;
+    const int units = m_units * ((N + BN - 1) / BN);
+    int grid = units * kCluster;
+    if (grid > max_ctas) grid = max_ctas;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = Cfg<BN, kCluster>::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    TFOP_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc,
+                                 out_dtype, epi, a_mn, b_mn));
     return 0;
 }
 
@@ -509,18 +622,28 @@ TFOP_API int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* b
     // K-major: rows = MN extent, inner = K, box [BLOCK_M | tile_n rows, 64]
     // MN-major: rows = K extent, inner = MN, box [64 k-rows, 64]
     if (a_mn ? make_map(&ma, A, K, M, lda, BLOCK_K) : make_map(&ma, A, M, K, lda, BLOCK_M)) return -1;
-    if (b_mn ? make_map(&mb, B, K, N, ldb, BLOCK_K) : make_map(&mb, B, N, K, ldb, tile_n)) return -1;
+    // CTA pairs (cta_group::2) take two vertically adjacent m-blocks: worth it from two m-blocks on
+    const int m_blocks = (M + BLOCK_M - 1) / BLOCK_M;
+    const bool cluster = g_cluster_mode == 1 || (g_cluster_mode == -1 && m_blocks >= 2);
+    // (a K-major B box is the part one CTA fetches: the whole tile, or half of it per CTA)
+    if (b_mn ? make_map(&mb, B, K, N, ldb, BLOCK_K)
+             : make_map(&mb, B, N, K, ldb, cluster ? tile_n / 2 : tile_n))
+        return -1;
     // TMA can describe C when its row pitch and base are 16-byte multiples
     const int elt = out_dtype == TFOP_BF16 ? 2 : 4;
     const bool tma_store = !g_force_direct_store && ((size_t)ldc * elt) % 16 == 0 &&
                            (((uintptr_t)C) & 15) == 0;
     CUtensorMap mc = ma;
     if (tma_store && make_map_c(&mc, C, M, N, ldc, out_dtype) != 0) return -1;
-#define TFOP_GEMM_LAUNCH(BN_, TMA_)                                                             \
-    launch<BN_, TMA_>(ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, a_mn, \
-                      b_mn, stream)
-    if (tile_n == 256) return tma_store ? TFOP_GEMM_LAUNCH(256, true) : TFOP_GEMM_LAUNCH(256, false);
-    return tma_store ? TFOP_GEMM_LAUNCH(128, true) : TFOP_GEMM_LAUNCH(128, false);
+#define TFOP_GEMM_LAUNCH(BN_, TMA_, CL_)                                                       \
+    launch<BN_, TMA_, CL_>(ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, \
+                           a_mn, b_mn, stream)
+#define TFOP_GEMM_LAUNCH2(BN_, TMA_) \
+    (cluster ? TFOP_GEMM_LAUNCH(BN_, TMA_, 2) : TFOP_GEMM_LAUNCH(BN_, TMA_, 1))
+    if (tile_n == 256)
+        return tma_store ? TFOP_GEMM_LAUNCH2(256, true) : TFOP_GEMM_LAUNCH2(256, false);
+    return tma_store ? TFOP_GEMM_LAUNCH2(128, true) : TFOP_GEMM_LAUNCH2(128, false);
+#undef TFOP_GEMM_LAUNCH2
 #undef TFOP_GEMM_LAUNCH
 }
 
@@ -530,6 +653,14 @@ TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void
                                int out_dtype, int epilogue, int tile_n, cudaStream_t stream) {
     return tfop_gemm_bf16(A, B, C, bias, bias_dtype, M, N, K, lda, ldb, ldc, out_dtype, epilogue,
                           tile_n, 0, 0, stream);
+}
+
+// Benchmark / test hook: -1 auto (default), 0 never, 1 always run the CTAs as cta_group::2
+// pairs (256-row MMAs, each SM staging half of the B tile).
+TFOP_API int tfop_gemm_set_cluster_mode(int mode) {
+    TFOP_REQUIRE(mode >= -1 && mode <= 1, "cluster mode must be -1, 0 or 1");
+    g_cluster_mode = mode;
+    return 0;
 }
 
 // Test hook: 1 forces the direct (per-thread 16-byte) C stores even where TMA stores apply.
