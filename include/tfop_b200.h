@@ -190,10 +190,24 @@ int tfop_ln_fwd(const void* h, const void* bias, const void* res, const void* ga
 int tfop_ln_bwd(const void* dy, const void* s, const float* mean, const float* rstd,
                 const void* gamma, void* dx, float* dgamma, float* dbeta, float* dbias, int rows,
                 int H, cudaStream_t stream);
+/* Test hook: 1 routes every LayerNorm backward through the warp-per-row kernel (the default for
+ * H % 256 == 0 is the tiled kernel: H/8 threads per row, 4 rows per thread and trip). */
+int tfop_ln_force_warp_rows(int on);
 int tfop_bias_gelu_fwd(const void* h, const void* bias, void* y, int rows, int H,
                        cudaStream_t stream);
 int tfop_bias_act_bwd(const void* dy, const void* h, const void* bias, void* dh, float* dbias,
                       int rows, int H, int act, cudaStream_t stream);
+
+/* ---- K10: softmax cross-entropy with ignore_index over bf16 logits (csrc/xent.cu) ----
+ * Mean over labelled rows (int64 labels). Forward reads only labelled rows and saves one fp32
+ * log-sum-exp per row; backward writes bf16 dlogits (zeros for unlabelled rows). inv_n and
+ * grad_out are device scalars. No reference counterpart (BASELINE.json config 3). */
+int tfop_xent_fwd(const void* logits, long ld, const void* labels, int rows, int V,
+                  long long ignore_index, const float* inv_n, float* row_loss, float* lse,
+                  cudaStream_t stream);
+int tfop_xent_bwd(const void* logits, long ld, const void* labels, int rows, int V,
+                  long long ignore_index, const float* inv_n, const float* lse,
+                  const float* grad_out, void* dlogits, long ld_out, cudaStream_t stream);
 
 /* bf16 transpose out[C,R] = in[R,C]^T (csrc/transpose.cu); feeds the K-major operands of the
  * weight-gradient GEMM. No reference counterpart. */

@@ -7,10 +7,23 @@ import torch.nn.functional as F
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("rows,H", [(515, 1024), (64, 128), (1000, 768), (33, 1536), (8192, 1024)])
+@pytest.mark.parametrize("rows,H", [(515, 1024), (64, 128), (1000, 768), (33, 1536), (8192, 1024),
+                                    (100, 520), (7, 256)])
 @pytest.mark.parametrize("with_bias,with_res", [(True, True), (False, False), (True, False)])
-def test_add_bias_layernorm_matches_fp32(rows, H, with_bias, with_res):
+@pytest.mark.parametrize("warp_rows", [False, True])
+def test_add_bias_layernorm_matches_fp32(rows, H, with_bias, with_res, warp_rows):
+    from tf_operator_b200.ops import _lib
     from tf_operator_b200.ops.layernorm import add_bias_layernorm
+    if warp_rows and H % 256:
+        pytest.skip("the warp-per-row backward is already the default for this hidden size")
+    _lib.load().tfop_ln_force_warp_rows(1 if warp_rows else 0)
+    try:
+        _ln_case(add_bias_layernorm, rows, H, with_bias, with_res)
+    finally:
+        _lib.load().tfop_ln_force_warp_rows(0)
+
+
+def _ln_case(add_bias_layernorm, rows, H, with_bias, with_res):
     torch.manual_seed(rows + H)
     dev = "cuda"
     h = torch.randn(rows, H, device=dev).bfloat16().requires_grad_(True)
@@ -96,3 +109,31 @@ def test_bert_tiny_fused_path_matches_stock_twin():
         gn, gs = pn.grad.float(), ps.grad.float()
         denom = gs.abs().max().item() + 1e-6
         assert (gn - gs).abs().max().item() / denom < 0.08, name
+
+
+@pytest.mark.parametrize("rows,V", [(512, 30528), (64, 1000), (33, 1027), (8, 8)])
+def test_softmax_cross_entropy_matches_fp32(rows, V):
+    from tf_operator_b200.ops.xent import softmax_cross_entropy
+    torch.manual_seed(rows + V)
+    logits = (torch.randn(rows, V, device="cuda") * 3).bfloat16().requires_grad_(True)
+    labels = torch.randint(0, V, (rows,), device="cuda")
+    labels[torch.rand(rows, device="cuda") < 0.6] = -100
+    labels[0] = 5 % V      # at least one labelled row
+    w = torch.tensor(0.7, device="cuda")
+    loss = softmax_cross_entropy(logits, labels, -100)
+    (loss * w).backward()
+    lf = logits.detach().float().requires_grad_(True)
+    ref = F.cross_entropy(lf, labels, ignore_index=-100)
+    (ref * w).backward()
+    torch.testing.assert_close(loss, ref, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(logits.grad.float(), lf.grad, rtol=2e-2, atol=1e-5)
+    assert bool((logits.grad[labels == -100] == 0).all())
+
+
+def test_softmax_cross_entropy_all_ignored():
+    from tf_operator_b200.ops.xent import softmax_cross_entropy
+    logits = torch.randn(16, 64, device="cuda").bfloat16().requires_grad_(True)
+    labels = torch.full((16,), -100, device="cuda", dtype=torch.int64)
+    loss = softmax_cross_entropy(logits, labels, -100)
+    loss.backward()
+    assert float(loss) == 0.0 and bool((logits.grad == 0).all())

@@ -16,6 +16,7 @@ import torch.nn.functional as F
 
 from ..ops.gemm import TcLinear, linear
 from ..ops.layernorm import add_bias_layernorm, bias_gelu
+from ..ops.xent import softmax_cross_entropy
 
 
 @dataclass
@@ -140,8 +141,12 @@ class BertForPreTraining(nn.Module):
         else:
             h = self.mlm_ln(self.mlm_dense(x))
             logits = F.linear(h, self.tok.weight, self.mlm_bias)
-        mlm = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1),
-                              ignore_index=-100)
+        if self.cfg.tc_gemm:
+            # fused kernel: reads only the labelled rows, writes bf16 dlogits (ops/xent.py)
+            mlm = softmax_cross_entropy(logits.view(-1, logits.shape[-1]), mlm_labels.view(-1), -100)
+        else:
+            mlm = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1),
+                                  ignore_index=-100)
         pooled = torch.tanh(self.pooler(x[:, 0]))
         nsp = F.cross_entropy(self.nsp(pooled)[..., :2].float(), nsp_labels)
         return mlm + nsp

@@ -95,9 +95,14 @@ _SIGS = {
                             c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
     "tfop_ln_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "tfop_ln_force_warp_rows": (c_int, [c_int]),
     "tfop_bias_gelu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "tfop_bias_act_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                   c_int, c_void_p]),
+    "tfop_xent_fwd": (c_int, [c_void_p, C.c_long, c_void_p, c_int, c_int, C.c_longlong, c_void_p,
+                              c_void_p, c_void_p, c_void_p]),
+    "tfop_xent_bwd": (c_int, [c_void_p, C.c_long, c_void_p, c_int, c_int, C.c_longlong, c_void_p,
+                              c_void_p, c_void_p, c_void_p, C.c_long, c_void_p]),
     "tfop_transpose_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
