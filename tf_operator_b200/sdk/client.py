@@ -53,6 +53,9 @@ class JobClient:
 
     def __init__(self, config_file=None, context=None, client_configuration=None,
                  persist_config=True, *, cluster=None, transport=None):
+        """Connect to an API server: ``cluster=`` an in-process LocalCluster, ``transport=`` an
+        explicit transport, else ``$TFOP_APISERVER`` (REST) or the process-wide default cluster.
+        The kubeconfig arguments of the reference signature are accepted and ignored."""
         # config_file / context / client_configuration / persist_config are accepted for
         # signature compatibility with the reference; there is no kubeconfig on one box.
         mod = module_for(self.KIND)
@@ -108,6 +111,7 @@ class JobClient:
             raise self._err("CustomObjectsApi->get_namespaced_custom_object", e) from e
 
     def patch(self, name, job, namespace=None):
+        """Merge-patch the named job with ``job`` (dict or model); returns the patched object."""
         if namespace is None:
             namespace = utils.set_job_namespace(job)
         try:
@@ -116,6 +120,7 @@ class JobClient:
             raise self._err("CustomObjectsApi->patch_namespaced_custom_object", e) from e
 
     def delete(self, name, namespace=None):
+        """Delete the named job; its pods and services go with it (owner references)."""
         if namespace is None:
             namespace = utils.get_default_target_namespace()
         try:
@@ -168,14 +173,18 @@ class JobClient:
         return last.get("type", "")
 
     def is_job_running(self, name, namespace=None) -> bool:
+        """True when the last condition is Running."""
         return self.get_job_status(name, namespace=namespace).lower() == "running"
 
     def is_job_succeeded(self, name, namespace=None) -> bool:
+        """True when the last condition is Succeeded."""
         return self.get_job_status(name, namespace=namespace).lower() == "succeeded"
 
     # ---- pods / logs -------------------------------------------------------------
     def get_pod_names(self, name, namespace=None, master=False, replica_type=None,
                       replica_index=None):
+        """Set of pod names of the job, filtered by master role / replica type / replica index
+        through the controller's labels; None (with a warning) when nothing matches."""
         if namespace is None:
             namespace = utils.get_default_target_namespace()
         labels = utils.get_labels(name, master=master, replica_type=replica_type,
