@@ -30,6 +30,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "nccl"])
     ap.add_argument("--no-graph", action="store_true", help="run eager instead of one CUDA graph per step")
+    ap.add_argument("--ckpt", default="", help="checkpoint file (a mounted path in the pod template): "
+                    "loaded at start when it exists, written by rank 0 at the end - a replica the "
+                    "operator restarts under the same name resumes from it")
     args = ap.parse_args()
 
     ctx = ReplicaContext.from_env()
@@ -63,6 +66,9 @@ def main():
         comm = ctx.symmetric_comm(nparam * 2 + (8 << 20)) if ctx.world_size > 1 else None
         dp = FlatDataParallel(model, comm=comm, optimizer="adamw", lr=1e-4, weight_decay=0.01,
                               bucket_bytes=64 << 20)
+
+        if args.ckpt and os.path.exists(args.ckpt):
+            print(json.dumps({"resumed_from_step": dp.load_checkpoint(args.ckpt)}), flush=True)
 
         graph = {"g": None, "loss": None}
 
@@ -107,6 +113,8 @@ def main():
            "seq_per_s_job": round(B * ctx.world_size / ms * 1e3, 1), "loss": round(float(loss), 4),
            "kernel_launches_per_step": launches()}
     print(json.dumps(out), flush=True)
+    if args.ckpt and args.impl == "native" and ctx.rank == 0:
+        dp.save_checkpoint(args.ckpt)
     time.sleep(0.5)
     return 0
 

@@ -35,3 +35,48 @@ def test_is_dense():
     assert _is_dense(torch.zeros(4, 3, 2, 2))
     assert _is_dense(torch.zeros(4, 3, 2, 2).contiguous(memory_format=torch.channels_last))
     assert not _is_dense(torch.zeros(4, 6)[:, ::2])
+
+
+def test_named_export_import_roundtrip_across_bucket_layouts():
+    """A checkpoint is keyed by parameter name: it loads into an engine whose flat layout
+    (bucket size, memory format) differs from the writer's."""
+    torch.manual_seed(1)
+    m1 = ResNet(18, num_classes=10, width=16, fused=False).to(memory_format=torch.channels_last)
+    fp1 = FlatParams(m1, torch.device("cpu"), bucket_bytes=64 << 10)
+    mom1 = torch.randn(fp1.total)
+    named_w, named_m = fp1.export_named(fp1.master), fp1.export_named(mom1)
+    assert set(named_w) == {n for n, _ in m1.named_parameters()}
+    assert all(t.is_contiguous() and t.device.type == "cpu" for t in named_w.values())
+
+    torch.manual_seed(2)
+    m2 = ResNet(18, num_classes=10, width=16, fused=False)      # different init, NCHW layout
+    fp2 = FlatParams(m2, torch.device("cpu"), bucket_bytes=1 << 20)
+    mom2 = torch.zeros(fp2.total)
+    assert fp2.import_named(fp2.master, named_w) == []
+    fp2.refresh_weights()
+    fp2.import_named(mom2, named_m)
+    for (n1, p1), (n2, p2) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert n1 == n2 and torch.equal(p1.float(), p2.float()), n1
+    for s in fp2.slots:
+        assert torch.equal(fp2.view_of(mom2, s), named_m[s.name])
+        assert torch.equal(fp2.view_of(fp2.master, s), named_w[s.name])
+    # the exported weights load into a plain module too
+    m3 = ResNet(18, num_classes=10, width=16, fused=False)
+    missing, unexpected = m3.load_state_dict(named_w, strict=False)
+    assert unexpected == [] and all("running_" in k or "num_batches" in k for k in missing)
+
+
+def test_import_named_reports_missing_and_shape_errors():
+    import pytest
+    m = ResNet(18, num_classes=10, width=16, fused=False)
+    fp = FlatParams(m, torch.device("cpu"))
+    named = fp.export_named(fp.master)
+    first = next(iter(named))
+    partial = {k: v for k, v in named.items() if k != first}
+    with pytest.raises(KeyError):
+        fp.import_named(fp.master, partial)
+    assert fp.import_named(fp.master, partial, strict=False) == [first]
+    bad = dict(named)
+    bad[first] = torch.zeros(3)
+    with pytest.raises(ValueError):
+        fp.import_named(fp.master, bad)

@@ -176,6 +176,61 @@ class FlatDataParallel:
         self._hp_host[0] = lr
         self.hp.copy_(self._hp_host, non_blocking=True)
 
+    # ------------------------------------------------------------------ checkpoint / resume
+    # The reference operator never touches model state: resume works by
+    # convention - stable replica names and a user-mounted path, as in the Keras example
+    # (examples/v1/distribution_strategy/keras-API/multi_worker_strategy-with-keras.py:91-110).
+    # This is the runtime half of that convention: a replica restarted by the operator under the
+    # same name calls load_checkpoint() and continues from the saved step.
+    def state_dict(self) -> dict:
+        """fp32 master weights, optimizer moments (keyed by parameter name, CPU tensors), module
+        buffers, hyper-parameters and the step counter. ``sd["model"]`` loads into the plain
+        ``nn.Module`` with ``load_state_dict(..., strict=False)``."""
+        torch.cuda.current_stream().synchronize()
+        sd = {"version": 1, "optimizer": self.optimizer, "step": int(self._steps),
+              "hp": [float(x) for x in self._hp_host.tolist()],
+              "model": self.flat.export_named(self.flat.master),
+              "mom": self.flat.export_named(self.mom),
+              "buffers": {n: b.detach().to("cpu", copy=True) for n, b in self.model.named_buffers()}}
+        if self.mom2 is not None:
+            sd["mom2"] = self.flat.export_named(self.mom2)
+        return sd
+
+    def load_state_dict(self, sd: dict, strict: bool = True) -> None:
+        if sd.get("optimizer", self.optimizer) != self.optimizer:
+            raise ValueError(f"checkpoint was written by optimizer {sd['optimizer']!r}, "
+                             f"this engine runs {self.optimizer!r}")
+        self.flat.import_named(self.flat.master, sd["model"], strict)
+        self.flat.refresh_weights()
+        self.flat.import_named(self.mom, sd.get("mom", {}), strict)
+        if self.mom2 is not None:
+            self.flat.import_named(self.mom2, sd.get("mom2", {}), strict)
+        with torch.no_grad():
+            bufs = dict(self.model.named_buffers())
+            for n, t in sd.get("buffers", {}).items():
+                if n in bufs:
+                    bufs[n].copy_(t.to(bufs[n].device, dtype=bufs[n].dtype))
+        self._steps = int(sd.get("step", 0))
+        hp = sd.get("hp")
+        if hp:
+            self._hp_host.copy_(torch.tensor(hp, dtype=torch.float32))
+            self.hp.copy_(self._hp_host)
+        torch.cuda.current_stream().synchronize()
+
+    def save_checkpoint(self, path: str) -> None:
+        """Atomic write (tmp + rename): a replica killed mid-save leaves the previous file. In a
+        data-parallel job every rank holds the same state, so rank 0 (chief / master) saves."""
+        import os
+        tmp = f"{path}.tmp.{os.getpid()}"
+        torch.save(self.state_dict(), tmp)
+        os.replace(tmp, path)
+
+    def load_checkpoint(self, path: str, strict: bool = True) -> int:
+        """Load a checkpoint written by save_checkpoint; returns the step to resume from."""
+        sd = torch.load(path, map_location="cpu", weights_only=False)
+        self.load_state_dict(sd, strict)
+        return self._steps
+
 
 class DataParallelEngine(FlatDataParallel):
     def __init__(self, model: nn.Module, *, comm: Optional[SymmetricComm] = None,

@@ -103,6 +103,40 @@ class FlatParams:
         p = s.param
         return torch.as_strided(self.grads, p.shape, p.stride(), s.offset)
 
+    # ---- checkpoint support: flat buffers <-> per-parameter tensors keyed by name ----------
+    def view_of(self, flat: torch.Tensor, s: Slot) -> torch.Tensor:
+        """The slot's region of a flat buffer, shaped and strided like the parameter."""
+        p = s.param
+        return torch.as_strided(flat, p.shape, p.stride(), s.offset)
+
+    def export_named(self, flat: torch.Tensor) -> dict:
+        """{parameter name: contiguous CPU copy} of one flat buffer (master weights, momentum...).
+        Layout-independent, so a checkpoint survives a change of bucket size or parameter order."""
+        return {s.name: self.view_of(flat, s).detach().to("cpu", copy=True).contiguous()
+                for s in self.slots}
+
+    def import_named(self, flat: torch.Tensor, named: dict, strict: bool = True) -> List[str]:
+        """Copy per-parameter tensors back into a flat buffer; returns the names not found."""
+        missing = []
+        with torch.no_grad():
+            for s in self.slots:
+                if s.name not in named:
+                    missing.append(s.name)
+                    continue
+                src = named[s.name]
+                if tuple(src.shape) != tuple(s.param.shape):
+                    raise ValueError(f"checkpoint shape {tuple(src.shape)} != parameter shape "
+                                     f"{tuple(s.param.shape)} for {s.name}")
+                self.view_of(flat, s).copy_(src.to(flat.device, dtype=flat.dtype))
+        if strict and missing:
+            raise KeyError(f"checkpoint lacks parameters: {missing[:5]}{'...' if len(missing) > 5 else ''}")
+        return missing
+
+    def refresh_weights(self) -> None:
+        """Model-dtype weights := round(master) after the master buffer was loaded."""
+        with torch.no_grad():
+            self.weights.copy_(self.master.to(self.weight_dtype))
+
     def check_grad_layouts(self) -> List[str]:
         """Names of parameters whose .grad strides differ from the parameter's."""
         def sig(t):
