@@ -231,6 +231,8 @@ int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* bias, int 
  * CTAs as cta_group::2 pairs (2-CTA clusters; one tcgen05.mma covers 256 rows, each SM stages
  * only half of the B tile). */
 int tfop_gemm_set_cluster_mode(int mode);
+/* Benchmark hook: band height of the tile order, in scheduling units (0 = built-in default). */
+int tfop_gemm_set_group_m(int g);
 /* Test hook: 1 forces the per-thread direct C stores even where the TMA-store epilogue
  * (32x128-byte swizzled boxes, used when ldc*elt and C are 16-byte multiples) applies. */
 int tfop_gemm_force_direct_store(int on);

@@ -200,6 +200,16 @@ __device__ __forceinline__ void tile_coords_g(int t, int m_blocks, int n_blocks,
     mb = first_m + r % gm;
     nb = r / gm;
 }
+__device__ __forceinline__ void tile_coords_rt(int t, int m_blocks, int n_blocks, int group,
+                                               int& mb, int& nb) {
+    const int per_group = group * n_blocks;
+    const int g = t / per_group;
+    const int first_m = g * group;
+    const int gm = min(group, m_blocks - first_m);
+    const int r = t - g * per_group;
+    mb = first_m + r % gm;
+    nb = r / gm;
+}
 __device__ __forceinline__ void tile_coords(int t, int m_blocks, int n_blocks, int& mb, int& nb) {
     tile_coords_g<kGroupM>(t, m_blocks, n_blocks, mb, nb);
 }

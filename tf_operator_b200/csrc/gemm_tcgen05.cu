@@ -81,7 +81,7 @@ template <int BN, bool kTmaStore, int kCluster>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_c, void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
-               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn) {
+               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn, int group_m) {
     using cfg = Cfg<BN, kCluster>;
     constexpr bool kPair = kCluster == 2;
     extern __shared__ uint8_t smem_raw[];
@@ -104,7 +104,6 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int n_blocks = (N + BN - 1) / BN;
     const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
     // scheduling unit: one m-block, or a vertical pair of m-blocks per cluster
-    constexpr int kGroup = kCluster == 2 ? kGroupM / 2 : kGroupM;
     const int crank = kCluster == 2 ? (int)cluster_ctarank() : 0;
     const int m_units = (m_blocks + kCluster - 1) / kCluster;
     const int num_tiles = m_units * n_blocks;
@@ -156,7 +155,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             uint32_t phase = 0;
             for (int t = t_first; t < num_tiles; t += t_step) {
                 int mb, nb;
-                tile_coords_g<kGroup>(t, m_units, n_blocks, mb, nb);
+                tile_coords_rt(t, m_units, n_blocks, group_m, mb, nb);
                 const int m0 = (mb * kCluster + crank) * BLOCK_M;
                 const int n0 = nb * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
@@ -278,7 +277,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             int buf = 0;
             for (int t = t_first; t < num_tiles; t += t_step) {
                 int mb, nb;
-                tile_coords_g<kGroup>(t, m_units, n_blocks, mb, nb);
+                tile_coords_rt(t, m_units, n_blocks, group_m, mb, nb);
                 const int m0 = (mb * kCluster + crank) * BLOCK_M;
                 const int n0 = nb * BN;
                 if (epi != EPI_NONE)
@@ -375,7 +374,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         } else {
         for (int t = t_first; t < num_tiles; t += t_step) {
             int mb, nb;
-            tile_coords_g<kGroup>(t, m_units, n_blocks, mb, nb);
+            tile_coords_rt(t, m_units, n_blocks, group_m, mb, nb);
             const int m0 = (mb * kCluster + crank) * BLOCK_M;
             const int n0 = nb * BN;
             if (epi != EPI_NONE) stage_bias<BN>(sbias, bias, bias_dtype, n0, N, ew * 32 + lane);
@@ -515,6 +514,7 @@ int g_num_sms = 0;
 int g_force_direct_store = 0;
 
 int g_cluster_mode = -1;  // -1 auto, 0 off, 1 force clusters of two
+int g_group_m = 0;        // 0: default band height; > 0: override (benchmark hook)
 
 template <int BN, bool kTmaStore, int kCluster>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, void* C,
@@ -563,8 +563,19 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    // Band height in scheduling units (m-blocks, or pairs of m-blocks): as tall as keeps the
+    // band's A panel (rows x K) around 32 MB, i.e. resident in L2 while the wave sweeps N, so B
+    // is re-read once per band and A once. Measured (benchmarks/gemm_group_sweep.py): 8192^3
+    // best at 8 pairs (1.56 vs 1.45 PFLOP/s at 32), 8192x30528x1024 best at 32 (1.50 vs 1.36).
+    int group_m = g_group_m;
+    if (group_m <= 0) {
+        const long panel_row_bytes = (long)BLOCK_M * kCluster * K * 2;
+        group_m = (int)((32L << 20) / panel_row_bytes);
+        if (group_m < 2) group_m = 2;
+        if (group_m > m_units) group_m = m_units;
+    }
     TFOP_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc,
-                                 out_dtype, epi, a_mn, b_mn));
+                                 out_dtype, epi, a_mn, b_mn, group_m));
     return 0;
 }
 
@@ -660,6 +671,13 @@ TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void
 TFOP_API int tfop_gemm_set_cluster_mode(int mode) {
     TFOP_REQUIRE(mode >= -1 && mode <= 1, "cluster mode must be -1, 0 or 1");
     g_cluster_mode = mode;
+    return 0;
+}
+
+// Benchmark hook: band height of the tile order in scheduling units (0 = default).
+TFOP_API int tfop_gemm_set_group_m(int g) {
+    TFOP_REQUIRE(g >= 0 && g <= 1024, "group_m out of range");
+    g_group_m = g;
     return 0;
 }
 
