@@ -209,6 +209,19 @@ int tfop_xent_bwd(const void* logits, long ld, const void* labels, int rows, int
                   long long ignore_index, const float* inv_n, const float* lse,
                   const float* grad_out, void* dlogits, long ld_out, cudaStream_t stream);
 
+/* ---- K11: ResNet stem as an implicit GEMM on tcgen05 (csrc/conv_stem.cu) ----
+ * y[N,OH,OW,64] = conv4x4/1(x[N,OH+3,OW+3,16], w[64,4,4,16]), bf16 NHWC / KRSC; x comes from
+ * tfop_stem_space_to_depth. The im2col operand is read straight from x through a 5-D TMA map
+ * with overlapping windows; the 32 KB weight stays in shared memory. OH % 8 == 0, OW % 16 == 0.
+ * No reference counterpart (BASELINE.json config 2 names the model). */
+/* dw[64,4,4,16] fp32, zeroed by the caller: weight gradient of the stem (split-K over all CTAs,
+ * both operands MN-major straight from dy and the overlapping-window map of x, RED at the end). */
+int tfop_conv_stem_s2d_wgrad(const void* x, const void* dy, float* dw, int n, int oh, int ow,
+                             cudaStream_t stream);
+int tfop_conv_stem_set_mode(int mode); /* test hook: 0 = 4-D window map (SW128), 1 = 5-D (SW32) */
+int tfop_conv_stem_s2d_fwd(const void* x, const void* w, void* y, int n, int oh, int ow,
+                           cudaStream_t stream);
+
 /* bf16 transpose out[C,R] = in[R,C]^T (csrc/transpose.cu); feeds the K-major operands of the
  * weight-gradient GEMM. No reference counterpart. */
 int tfop_transpose_bf16(const void* in, void* out, int R, int C, int ld_in, int ld_out,

@@ -226,3 +226,34 @@ def test_transpose_bf16(r, c):
     assert torch.equal(transpose(x), x.t().contiguous())
     xs = torch.randn(r, c + 8, device="cuda").bfloat16()[:, :c]     # strided rows
     assert torch.equal(transpose(xs), xs.t().contiguous())
+
+
+@pytest.mark.parametrize("n,img", [(2, 64), (3, 224), (16, 32)])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_conv_stem_s2d_matches_cudnn_and_fp32(gemm_ok, n, img, mode):
+    """The stem as a tcgen05 implicit GEMM (5-D TMA map with overlapping windows) against the
+    fp32 convolution of the same bf16 inputs, forward and weight gradient."""
+    from tf_operator_b200.ops.conv_stem import _eligible, stem_conv_s2d
+    from tf_operator_b200.ops.preproc import stem_space_to_depth, stem_weight_s2d
+    torch.manual_seed(n + img)
+    u8 = torch.randint(0, 256, (n, img, img, 3), dtype=torch.uint8, device="cuda")
+    x = stem_space_to_depth(u8)                                    # [n,16,img/2+3,img/2+3] NHWC
+    w7 = (torch.randn(64, 3, 7, 7, device="cuda") * 0.05).bfloat16().requires_grad_(True)
+    w4 = stem_weight_s2d(w7)
+    assert _eligible(x, w4)
+    from tf_operator_b200.ops import _lib
+    _lib.load().tfop_conv_stem_set_mode(mode)
+    try:
+        y = stem_conv_s2d(x, w4)
+        torch.cuda.synchronize()
+    finally:
+        _lib.load().tfop_conv_stem_set_mode(0)
+    ref = F.conv2d(x.float(), w4.detach().float())
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    torch.testing.assert_close(y.float(), ref, rtol=2e-2, atol=3e-2)
+    # equals the original 7x7 / stride 2 / pad 3 convolution of the normalised image
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    w7f = w7.detach().float().requires_grad_(True)
+    F.conv2d(x.float(), stem_weight_s2d(w7f)).backward(dy.float())
+    torch.testing.assert_close(w7.grad.float(), w7f.grad, rtol=5e-2, atol=0.05 * (n * img * img / 4) ** 0.5)

@@ -14,6 +14,7 @@ import torch.nn.functional as F
 
 from ..ops.bn import FusedBatchNorm2d
 from ..ops.pool import MaxPool3x3s2
+from ..ops.conv_stem import stem_conv_s2d
 from ..ops.preproc import stem_weight_s2d
 
 
@@ -112,7 +113,8 @@ class ResNet(nn.Module):
         if x.shape[1] == 16:
             # input already in the stem's space-to-depth layout (ops/preproc.py): the 7x7/2
             # convolution runs as a 4x4/1 convolution over 16 channels, same parameters
-            x = F.conv2d(x, stem_weight_s2d(self.conv1.weight))
+            # tcgen05 implicit GEMM when the shape allows it (ops/conv_stem.py), else cuDNN
+            x = stem_conv_s2d(x, stem_weight_s2d(self.conv1.weight))
         else:
             x = self.conv1(x)
         x = self.pool(self.bn1(x))

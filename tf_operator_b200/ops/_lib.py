@@ -104,6 +104,9 @@ _SIGS = {
                               c_void_p, c_void_p, c_void_p]),
     "tfop_xent_bwd": (c_int, [c_void_p, C.c_long, c_void_p, c_int, c_int, C.c_longlong, c_void_p,
                               c_void_p, c_void_p, c_void_p, C.c_long, c_void_p]),
+    "tfop_conv_stem_s2d_wgrad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "tfop_conv_stem_set_mode": (c_int, [c_int]),
+    "tfop_conv_stem_s2d_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "tfop_transpose_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
