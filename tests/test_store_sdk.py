@@ -235,3 +235,42 @@ def test_topology_placement():
                            GpuInfo(2, nvlink_peers={3: 4}), GpuInfo(3, nvlink_peers={2: 4})])
     assert pairs.pick(2, [0, 2, 3]) == [2, 3]
     assert pairs.pick(2, [0, 1, 2]) == [0, 1]
+
+
+def test_swagger_runtime_standins_roundtrip_models_over_rest():
+    """ApiClient / Configuration / rest: raw REST with the SDK models against
+    the REST facade - serialise a V1TFJob to camelCase JSON, POST, GET back as a model."""
+    from tf_operator_b200.cluster import LocalCluster
+    from tf_operator_b200.launcher.topology import synthetic
+    from tf_operator_b200.sdk import (ApiClient, ApiException, Configuration, V1Container, V1ObjectMeta,
+                                      V1PodSpec, V1PodTemplateSpec, V1ReplicaSpec, V1TFJob, V1TFJobSpec)
+    with LocalCluster(topology=synthetic(0), serve_http=True) as cl:
+        cfg = Configuration()
+        cfg.host = cl.api.url
+        Configuration.set_default(cfg)
+        api = ApiClient()
+        assert api.configuration.host == cl.api.url and "User-Agent" in api.default_headers
+        job = V1TFJob(api_version="kubeflow.org/v1", kind="TFJob",
+                      metadata=V1ObjectMeta(name="raw", namespace="default"),
+                      spec=V1TFJobSpec(tf_replica_specs={"Worker": V1ReplicaSpec(
+                          replicas=2, restart_policy="Never", template=V1PodTemplateSpec(spec=V1PodSpec(
+                              containers=[V1Container(name="tensorflow", image="x", command=["true"])])))}))
+        wire = api.sanitize_for_serialization(job)
+        assert wire["spec"]["tfReplicaSpecs"]["Worker"]["restartPolicy"] == "Never"
+        path = "/apis/kubeflow.org/v1/namespaces/{namespace}/tfjobs"
+        created = api.call_api(path, "POST", path_params={"namespace": "default"}, body=job,
+                               response_type="V1TFJob")
+        assert isinstance(created, V1TFJob) and created.metadata.name == "raw"
+        got, status, _ = api.call_api(path + "/{name}", "GET", path_params={"namespace": "default", "name": "raw"},
+                                      response_type="V1TFJob", _return_http_data_only=False)
+        assert status == 200 and got.spec.tf_replica_specs["Worker"].replicas == 2
+        lst = api.call_api(path, "GET", path_params={"namespace": "default"}, response_type="V1TFJobList")
+        assert [j.metadata.name for j in lst.items] == ["raw"]
+        import pytest
+        with pytest.raises(ApiException) as ei:
+            api.call_api(path + "/{name}", "GET", path_params={"namespace": "default", "name": "nope"})
+        assert ei.value.status == 404
+        assert api.select_header_accept(["application/yaml", "application/json"]) == "application/json"
+        assert api.select_header_content_type([]) == "application/json"
+        assert "SDK Package Version" in cfg.to_debug_report()
+    Configuration.set_default(None)

@@ -1,6 +1,9 @@
 """Python SDK: kubeflow.tfjob-compatible TFJobClient plus PyTorchJobClient / MXJobClient /
 XGBoostJobClient (sdk/python/kubeflow/tfjob/__init__.py:17-36 for the exported names)."""
 from . import constants, utils
+from .api_client import ApiClient
+from .configuration import Configuration
+from .rest import ApiException
 from .client import JobClient, MXJobClient, PyTorchJobClient, TFJobClient, XGBoostJobClient
 from .models import (V1Container, V1ContainerPort, V1EnvVar, V1JobCondition, V1JobStatus,
                      V1MXJob, V1MXJobList, V1MXJobSpec, V1ObjectMeta, V1PodSpec,
