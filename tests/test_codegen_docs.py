@@ -59,3 +59,29 @@ def test_setup_script_starts_the_operator_and_the_sdk_reaches_it(tmp_path):
         assert out.stdout.strip() == "PyTorchJobList", out.stdout + out.stderr
     finally:
         os.kill(pid, signal.SIGTERM)
+
+
+def test_py_checks_and_release_tooling(tmp_path):
+    """hack/py_checks.py (every .py compiles, junit report) and hack/release.py (tarball +
+    checksum manifest) - the reference's py_checks.py / release.py re-expressed for one box."""
+    import json
+    import tarfile
+    from xml.etree import ElementTree as ET
+    junit = tmp_path / "junit.xml"
+    res = subprocess.run([sys.executable, "hack/py_checks.py", "--no-tests", "--junit_path", str(junit)],
+                         cwd=REPO, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:]
+    root = ET.parse(junit).getroot()
+    assert int(root.attrib["tests"]) > 80 and root.attrib["failures"] == "0"
+    out = tmp_path / "dist"
+    res = subprocess.run([sys.executable, "hack/release.py", "--out", str(out), "--no-build"], cwd=REPO,
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    meta = json.loads(res.stdout.strip().splitlines()[-1])
+    tar = out / meta["artifact"]
+    assert tar.exists() and meta["arch"] == "sm_100a" and len(meta["sha256"]) == 64
+    with tarfile.open(tar) as t:
+        names = t.getnames()
+    assert any(n.endswith("tf_operator_b200/csrc/gemm_tcgen05.cu") for n in names)
+    assert any(n.endswith("manifests/base/kubeflow.org_tfjobs.yaml") for n in names)
+    assert not any("__pycache__" in n for n in names)
