@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "nccl"])
     ap.add_argument("--no-graph", action="store_true", help="run eager instead of one CUDA graph per step")
+    ap.add_argument("--no-nvls", action="store_true",
+                    help="reduce gradient buckets with the P2P two-shot kernel instead of NVLS multimem")
     ap.add_argument("--ckpt", default="", help="checkpoint file (a mounted path in the pod template): "
                     "loaded at start when it exists, written by rank 0 at the end - a replica the "
                     "operator restarts under the same name resumes from it")
@@ -49,6 +51,7 @@ def main():
     labels = torch.where(torch.rand(B, S, device=dev, generator=g) < 0.15, ids, torch.full_like(ids, -100))
     nsp = torch.randint(0, 2, (B,), device=dev, generator=g)
 
+    use_nvls = False
     if args.impl == "nccl":
         if ctx.world_size > 1:
             ctx.init_process_group("nccl")
@@ -63,9 +66,15 @@ def main():
             return loss.detach()
         launches = lambda: 0  # noqa: E731
     else:
-        comm = ctx.symmetric_comm(nparam * 2 + (8 << 20)) if ctx.world_size > 1 else None
+        comm = None
+        if ctx.world_size > 1:
+            # gradient bucket in symmetric memory; with NVLS it is also bound to a multicast
+            # object so the NVSwitch reduces it in place (comm.nvls_bytes == 0 when unsupported)
+            comm = ctx.symmetric_comm(nparam * 2 + (8 << 20),
+                                      nvls_bytes=0 if args.no_nvls else nparam * 2 + (1 << 20))
+        use_nvls = comm is not None and getattr(comm, "nvls_bytes", 0) > 0
         dp = FlatDataParallel(model, comm=comm, optimizer="adamw", lr=1e-4, weight_decay=0.01,
-                              bucket_bytes=64 << 20)
+                              bucket_bytes=64 << 20, use_nvls=use_nvls)
 
         if args.ckpt and os.path.exists(args.ckpt):
             print(json.dumps({"resumed_from_step": dp.load_checkpoint(args.ckpt)}), flush=True)
@@ -111,7 +120,10 @@ def main():
            "model": f"bert-{args.model}", "params_M": round(nparam / 1e6, 1), "seq_len": S,
            "per_gpu_batch": B, "ms_per_step": round(ms, 3),
            "seq_per_s_job": round(B * ctx.world_size / ms * 1e3, 1), "loss": round(float(loss), 4),
-           "kernel_launches_per_step": launches()}
+           "kernel_launches_per_step": launches(),
+           "allreduce": ("nvls" if (args.impl == "native" and ctx.world_size > 1 and use_nvls) else
+                         "p2p two-shot" if (args.impl == "native" and ctx.world_size > 1) else
+                         "nccl" if ctx.world_size > 1 else None)}
     print(json.dumps(out), flush=True)
     if args.ckpt and args.impl == "native" and ctx.rank == 0:
         dp.save_checkpoint(args.ckpt)

@@ -77,8 +77,13 @@ __device__ __forceinline__ void stage_bias(float* sbias, const void* bias, int b
 // even CTA issues MMAs; TMA loads of both CTAs count on its `full` barrier, its commits are
 // multicast to both CTAs' `empty` / `tmem_full` barriers, and both epilogues arrive on its
 // `tmem_empty`.
+// Register cap 128 (not the 255 that __launch_bounds__(256, 1) would allow): the CTA then holds
+// 32 K of the SM's 64 K registers, which leaves room for a 512-thread block of the all-reduce /
+// pack kernels to be resident NEXT TO a GEMM CTA - with 241 registers the gradient all-reduce of
+// a data-parallel step could only run between GEMMs (+1.1 ms per BERT-large step at 2 and at 8
+// GPUs alike).
 template <int BN, bool kTmaStore, int kCluster>
-__global__ void __launch_bounds__(kNumThreads, 1)
+__global__ void __maxnreg__(128)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_c, void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
                int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn, int group_m) {
