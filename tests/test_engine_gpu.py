@@ -66,3 +66,42 @@ def test_checkpoint_resume_reproduces_the_uninterrupted_run(tmp_path, graph):
     sd = torch.load(path, weights_only=False)
     assert sd["step"] == 6 and sd["optimizer"] == "sgd" and "fc.weight" in sd["model"]
     assert any("running_mean" in k for k in sd["buffers"])
+
+
+def test_linear_weight_gradients_land_in_the_bucket_without_a_pack_copy():
+    """TcLinear's wgrad GEMM stores dW straight into the flat gradient bucket (GradTarget);
+    autograd adopts that view as .grad, the pack step skips it, and training matches a twin
+    engine whose parameters have no direct target (everything packed)."""
+    import torch.nn as nn
+    from tf_operator_b200.ops.gemm import TcLinear
+    from tf_operator_b200.parallel.engine import FlatDataParallel
+
+    def make():
+        torch.manual_seed(5)
+        return nn.Sequential(TcLinear(256, 512, act="gelu"), TcLinear(512, 256), TcLinear(256, 64)).cuda().bfloat16()
+    x = torch.randn(128, 256, device="cuda").bfloat16()
+    t = torch.randn(128, 64, device="cuda")
+    ma, mb = make(), make()
+    ea = FlatDataParallel(ma, optimizer="adamw", lr=1e-3, weight_decay=0.0)
+    eb = FlatDataParallel(mb, optimizer="adamw", lr=1e-3, weight_decay=0.0)
+    for p in mb.parameters():
+        del p._tfop_grad_target                     # twin: classic path, every gradient packed
+    la = [float(ea.train_step(lambda: (ma(x).float() - t).pow(2).mean())) for _ in range(5)]
+    in_place = [s.name for s in ea.flat.slots if ea.flat.grad_in_place(s)]
+    assert sorted(in_place) == ["0.weight", "1.weight", "2.weight"], in_place
+    lb = [float(eb.train_step(lambda: (mb(x).float() - t).pow(2).mean())) for _ in range(5)]
+    assert not any(eb.flat.grad_in_place(s) for s in eb.flat.slots)
+    assert la == pytest.approx(lb, rel=1e-3, abs=1e-4), (la, lb)
+    torch.testing.assert_close(ea.flat.master, eb.flat.master, rtol=1e-3, atol=1e-5)
+    assert la[-1] < la[0]
+    # a weight used twice in one step: the second use must not overwrite the first in the bucket
+    torch.manual_seed(6)
+    lin = TcLinear(64, 64).cuda().bfloat16()
+    ref = TcLinear(64, 64).cuda().bfloat16()
+    ref.load_state_dict(lin.state_dict())
+    ec = FlatDataParallel(lin, optimizer="sgd", lr=0.0, momentum=0.0, weight_decay=0.0)
+    z = torch.randn(32, 64, device="cuda").bfloat16()
+    ec.train_step(lambda: lin(lin(z)).float().pow(2).mean())
+    ref(ref(z)).float().pow(2).mean().backward()
+    got = ec.flat.view_of(ec.flat.grads, [s for s in ec.flat.slots if s.name == "weight"][0])
+    torch.testing.assert_close(got.float(), ref.weight.grad.float(), rtol=2e-2, atol=2e-3)

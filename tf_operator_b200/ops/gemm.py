@@ -134,7 +134,10 @@ class _LinearFn(torch.autograd.Function):
             dx = (gemm(dy2, w, b_t=True) if mn_ok else gemm_tn(dy2, transpose(w))).view(ctx.xshape)
         if ctx.needs_input_grad[1]:
             # dW[N,K] = dY^T @ X: both stored [tokens, *] -> both MN-major, contraction over rows
-            dw = (gemm(dy2, x2, a_t=True, b_t=True) if mn_ok
+            # a flat-buffer engine lets the GEMM store dW straight into the gradient bucket
+            target = getattr(w, "_tfop_grad_target", None)
+            out = target.take() if (target is not None and mn_ok and w.dtype == torch.bfloat16) else None
+            dw = (gemm(dy2, x2, a_t=True, b_t=True, out=out) if mn_ok
                   else gemm_tn(transpose(dy2), transpose(x2)))
         if ctx.has_bias and ctx.needs_input_grad[2]:
             from .layernorm import bias_grad

@@ -114,9 +114,11 @@ class FlatDataParallel:
         return hook
 
     def _reduce_bucket(self, b, stream):
-        srcs = [s.param.grad for s in b.slots if s.param.grad is not None]
-        offs = [s.offset for s in b.slots if s.param.grad is not None]
-        fopt.multi_pack_bf16(srcs, offs, self.flat.grads, 1.0, stream)
+        # gradients a producer wrote straight into the bucket (GradTarget) need no packing
+        todo = [s for s in b.slots if s.param.grad is not None and not self.flat.grad_in_place(s)]
+        if todo:
+            fopt.multi_pack_bf16([s.param.grad for s in todo], [s.offset for s in todo],
+                                 self.flat.grads, 1.0, stream)
         if self.world > 1:
             # in place on the symmetric gradient bucket: sum over ranks * 1/world
             if self.use_nvls:
@@ -130,6 +132,7 @@ class FlatDataParallel:
 
     # ------------------------------------------------------------------ step pieces
     def _begin(self):
+        self.flat.step_id += 1
         for p in self.model.parameters():
             p.grad = None
         for b in self.flat.buckets:

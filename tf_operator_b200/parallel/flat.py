@@ -43,6 +43,25 @@ class Bucket:
     pending: int = 0
 
 
+class GradTarget:
+    """Lets a producer write a parameter's gradient straight into its slot of the flat gradient
+    bucket (ops/gemm._LinearFn does, for weight gradients): ``take()`` hands out a fresh view of
+    the slot once per step - a second use of the same parameter in one step gets None and
+    produces an ordinary tensor that autograd adds in place. Autograd adopts the returned view
+    as ``param.grad`` without copying, and the engine's pack step skips gradients that already
+    live in the bucket."""
+
+    def __init__(self, flat: "FlatParams", slot: "Slot"):
+        self.flat, self.slot, self.used_step = flat, slot, -1
+
+    def take(self) -> Optional[torch.Tensor]:
+        if self.used_step == self.flat.step_id:
+            return None
+        self.used_step = self.flat.step_id
+        p = self.slot.param
+        return torch.as_strided(self.flat.grads, p.shape, p.stride(), self.slot.offset)
+
+
 class FlatParams:
     def __init__(self, model: nn.Module, device: torch.device, *, grad_buffer: Optional[torch.Tensor] = None,
                  bucket_bytes: int = 16 << 20, weight_dtype: torch.dtype = torch.bfloat16):
@@ -91,10 +110,19 @@ class FlatParams:
                 self.buckets.append(cur)
             cur.slots.append(s)
             cur.hi = s.offset + _pad8(s.numel)
+        # direct gradient targets (see GradTarget); step_id is bumped by the engine every step
+        self.step_id = 0
+        for s in self.slots:
+            s.param._tfop_grad_target = GradTarget(self, s)
         self._bucket_of = {}
         for b in self.buckets:
             for s in b.slots:
                 self._bucket_of[id(s.param)] = b
+
+    def grad_in_place(self, s: Slot) -> bool:
+        """True when the parameter's .grad already is its slot of the flat gradient buffer."""
+        g = s.param.grad
+        return g is not None and g.data_ptr() == self.grads.data_ptr() + s.offset * self.grads.element_size()
 
     def bucket_of(self, p: nn.Parameter) -> Bucket:
         return self._bucket_of[id(p)]
