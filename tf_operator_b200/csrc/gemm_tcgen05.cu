@@ -77,16 +77,16 @@ __device__ __forceinline__ void stage_bias(float* sbias, const void* bias, int b
 // even CTA issues MMAs; TMA loads of both CTAs count on its `full` barrier, its commits are
 // multicast to both CTAs' `empty` / `tmem_full` barriers, and both epilogues arrive on its
 // `tmem_empty`.
-// Register cap 128 (not the 255 that __launch_bounds__(256, 1) would allow): the CTA then holds
-// 32 K of the SM's 64 K registers, which leaves room for a 512-thread block of the all-reduce /
+// Register cap 136 (not the 255 that __launch_bounds__(256, 1) would allow): the CTA then holds
+// 34 K of the SM's 64 K registers, which leaves room for a 512-thread block of the all-reduce /
 // pack kernels to be resident NEXT TO a GEMM CTA - with 241 registers the gradient all-reduce of
 // a data-parallel step could only run between GEMMs (+1.1 ms per BERT-large step at 2 and at 8
 // GPUs alike).
 template <int BN, bool kTmaStore, int kCluster>
-__global__ void __maxnreg__(128)
+__global__ void __maxnreg__(136)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_c, void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
-               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn, int group_m) {
+               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn, int group_m, int splits) {
     using cfg = Cfg<BN, kCluster>;
     constexpr bool kPair = kCluster == 2;
     extern __shared__ uint8_t smem_raw[];
@@ -111,7 +111,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // scheduling unit: one m-block, or a vertical pair of m-blocks per cluster
     const int crank = kCluster == 2 ? (int)cluster_ctarank() : 0;
     const int m_units = (m_blocks + kCluster - 1) / kCluster;
-    const int num_tiles = m_units * n_blocks;
+    // split-K: a scheduling unit is (tile, K range); the `splits` units of a tile are adjacent
+    const int num_tiles = m_units * n_blocks * splits;
     const int t_first = blockIdx.x / kCluster;
     const int t_step = gridDim.x / kCluster;
 
@@ -160,10 +161,13 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             uint32_t phase = 0;
             for (int t = t_first; t < num_tiles; t += t_step) {
                 int mb, nb;
-                tile_coords_rt(t, m_units, n_blocks, group_m, mb, nb);
+                tile_coords_rt(t / splits, m_units, n_blocks, group_m, mb, nb);
                 const int m0 = (mb * kCluster + crank) * BLOCK_M;
                 const int n0 = nb * BN;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                const int sp = t % splits;
+                const int kb0 = (int)((long)k_blocks * sp / splits);
+                const int kb1 = (int)((long)k_blocks * (sp + 1) / splits);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem_a + stage * cfg::kABytes;
                     uint8_t* sb = smem_b + stage * cfg::kBBytes;
@@ -231,7 +235,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 tcgen05_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                const int sp = t % splits;
+                const int kb0 = (int)((long)k_blocks * sp / splits);
+                const int kb1 = (int)((long)k_blocks * (sp + 1) / splits);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full[stage], phase);
                     tcgen05_fence_after();
                     const uint32_t a_addr = smem_u32(smem_a + stage * cfg::kABytes);
@@ -243,9 +250,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         const uint64_t bdesc = b_mn ? make_smem_desc_mn(b_addr + k * b_step)
                                                     : make_smem_desc(b_addr + k * b_step);
                         if (kPair)
-                            umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                            umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
                         else
-                            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
                     }
                     // frees the smem slot when the MMAs retire (in both CTAs of a pair)
                     if (kPair)
@@ -282,7 +289,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             int buf = 0;
             for (int t = t_first; t < num_tiles; t += t_step) {
                 int mb, nb;
-                tile_coords_rt(t, m_units, n_blocks, group_m, mb, nb);
+                tile_coords_rt(t / splits, m_units, n_blocks, group_m, mb, nb);
                 const int m0 = (mb * kCluster + crank) * BLOCK_M;
                 const int n0 = nb * BN;
                 if (epi != EPI_NONE)
@@ -321,8 +328,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         fence_async_smem();
                         __syncwarp();
                         if (lane == 0) {
-                            if (n0 + c < N && m0 + ew * 32 < M)
-                                tma_store_2d(&map_c, box, n0 + c, m0 + ew * 32);
+                            if (n0 + c < N && m0 + ew * 32 < M) {
+                                if (splits > 1)
+                                    tma_reduce_add_2d(&map_c, box, n0 + c, m0 + ew * 32);
+                                else
+                                    tma_store_2d(&map_c, box, n0 + c, m0 + ew * 32);
+                            }
                             bulk_commit();
                         }
                         buf ^= 1;
@@ -354,7 +365,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     __syncwarp();
                     if (lane == 0) {
                         const int cc = out_dtype == TFOP_BF16 ? n0 + c : n0 + c + 32;
-                        if (cc < N && m0 + ew * 32 < M) tma_store_2d(&map_c, box, cc, m0 + ew * 32);
+                        if (cc < N && m0 + ew * 32 < M) {
+                            if (splits > 1)
+                                tma_reduce_add_2d(&map_c, box, cc, m0 + ew * 32);
+                            else
+                                tma_store_2d(&map_c, box, cc, m0 + ew * 32);
+                        }
                         bulk_commit();
                     }
                     buf ^= 1;
@@ -379,7 +395,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         } else {
         for (int t = t_first; t < num_tiles; t += t_step) {
             int mb, nb;
-            tile_coords_rt(t, m_units, n_blocks, group_m, mb, nb);
+            tile_coords_rt(t / splits, m_units, n_blocks, group_m, mb, nb);
             const int m0 = (mb * kCluster + crank) * BLOCK_M;
             const int n0 = nb * BN;
             if (epi != EPI_NONE) stage_bias<BN>(sbias, bias, bias_dtype, n0, N, ew * 32 + lane);
@@ -520,11 +536,12 @@ int g_force_direct_store = 0;
 
 int g_cluster_mode = -1;  // -1 auto, 0 off, 1 force clusters of two
 int g_group_m = 0;        // 0: default band height; > 0: override (benchmark hook)
+int g_splits = 0;         // 0: split-K heuristic, > 0: forced split count, -1: never split
 
 template <int BN, bool kTmaStore, int kCluster>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, void* C,
            const void* bias, int bias_dtype, int M, int N, int K, int ldc, int out_dtype, int epi,
-           int a_mn, int b_mn, cudaStream_t stream) {
+           int a_mn, int b_mn, int splits_req, bool can_split, cudaStream_t stream) {
     static bool attr_set = false;
     static int max_ctas = 0;
     auto kern = gemm_tn_kernel<BN, kTmaStore, kCluster>;
@@ -553,7 +570,33 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
         attr_set = true;
     }
     const int m_units = ((M + BLOCK_M - 1) / BLOCK_M + kCluster - 1) / kCluster;
-    const int units = m_units * ((N + BN - 1) / BN);
+    const int tiles = m_units * ((N + BN - 1) / BN);
+    // Split-K when the tiles alone leave much of the machine idle (small M x N, long K - the
+    // weight-gradient shapes): pick the split count with the best wave efficiency, 3 % penalty
+    // per extra split for the reduction traffic, at least 16 k-blocks per split. The partial
+    // tiles are added into a zeroed C by TMA reduce-add stores.
+    int splits = 1;
+    if (can_split) {
+        const int slots = max_ctas / kCluster;
+        const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+        if (splits_req > 0) {
+            splits = splits_req;
+        } else {
+            auto eff = [&](int s) {
+                const int u = tiles * s;
+                return (double)u / (double)(((u + slots - 1) / slots) * slots) - 0.03 * (s - 1);
+            };
+            if (eff(1) < 0.75)
+                for (int s = 2; s <= 4; ++s)
+                    if (k_blocks / s >= 16 && eff(s) > eff(splits) + 1e-9) splits = s;
+        }
+        if (splits > k_blocks) splits = k_blocks;
+        if (splits > 1) {
+            const size_t elt = out_dtype == TFOP_BF16 ? 2 : 4;
+            TFOP_CUDA(cudaMemset2DAsync(C, (size_t)ldc * elt, 0, (size_t)N * elt, (size_t)M, stream));
+        }
+    }
+    const int units = tiles * splits;
     int grid = units * kCluster;
     if (grid > max_ctas) grid = max_ctas;
     cudaLaunchConfig_t cfg = {};
@@ -580,7 +623,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
         if (group_m > m_units) group_m = m_units;
     }
     TFOP_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc,
-                                 out_dtype, epi, a_mn, b_mn, group_m));
+                                 out_dtype, epi, a_mn, b_mn, group_m, splits));
     return 0;
 }
 
@@ -653,7 +696,8 @@ TFOP_API int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* b
     if (tma_store && make_map_c(&mc, C, M, N, ldc, out_dtype) != 0) return -1;
 #define TFOP_GEMM_LAUNCH(BN_, TMA_, CL_)                                                       \
     launch<BN_, TMA_, CL_>(ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc, out_dtype, epilogue, \
-                           a_mn, b_mn, stream)
+                           a_mn, b_mn, g_splits, tma_store && epilogue == 0 && g_splits >= 0,  \
+                           stream)
 #define TFOP_GEMM_LAUNCH2(BN_, TMA_) \
     (cluster ? TFOP_GEMM_LAUNCH(BN_, TMA_, 2) : TFOP_GEMM_LAUNCH(BN_, TMA_, 1))
     if (tile_n == 256)
@@ -676,6 +720,13 @@ TFOP_API int tfop_gemm_bf16_tn(const void* A, const void* B, void* C, const void
 TFOP_API int tfop_gemm_set_cluster_mode(int mode) {
     TFOP_REQUIRE(mode >= -1 && mode <= 1, "cluster mode must be -1, 0 or 1");
     g_cluster_mode = mode;
+    return 0;
+}
+
+// Benchmark / test hook: split-K factor (0 = heuristic, -1 = never, n > 0 = force n splits).
+TFOP_API int tfop_gemm_set_splits(int s) {
+    TFOP_REQUIRE(s >= -1 && s <= 64, "splits out of range");
+    g_splits = s;
     return 0;
 }
 

@@ -90,6 +90,7 @@ _SIGS = {
     "tfop_gemm_force_direct_store": (c_int, [c_int]),
     "tfop_gemm_set_cluster_mode": (c_int, [c_int]),
     "tfop_gemm_set_group_m": (c_int, [c_int]),
+    "tfop_gemm_set_splits": (c_int, [c_int]),
     "tfop_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ln_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
