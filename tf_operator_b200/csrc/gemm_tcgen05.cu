@@ -1,19 +1,27 @@
-// K7: bf16 GEMM on the 5th-gen tensor cores, written directly against the
-// sm_100a ISA: TMA (cp.async.bulk.tensor) loads into 128B-swizzled shared
-// memory, tcgen05.mma issued by one elected thread, fp32 accumulators in TMEM
-// (double buffered so the epilogue of tile i overlaps the MMAs of tile i+1),
-// tcgen05.ld for the fused bias / GeLU / ReLU epilogue.
+// K7: bf16 GEMM on the 5th-gen tensor cores, written directly against the sm_100a ISA.
 //
-//   C[M,N] = act(A[M,K] * B[N,K]^T + bias[N])        ("TN": both K-major, i.e.
-//   torch.nn.functional.linear(x, W, b))
+//   C[M,N] = act(op(A) * op(B)^T + bias[N]),  fp32 accumulation in TMEM
+//   op(X) = X stored K-major ([rows, K]) or MN-major ([K, rows]) - so F.linear, its dgrad and its
+//   wgrad all read the tensors as they sit in memory (no transposed copies).
 //
-// Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer,
-// warp 2 = TMEM allocator, warps 4..7 = epilogue (one per 32 TMEM lanes).
+// Structure (persistent, warp-specialised, one CTA per SM, 256 threads):
+//   warp 0    TMA producer: cp.async.bulk.tensor into 128B-swizzled shared-memory stages
+//   warp 1    MMA issuer: one elected thread, tcgen05.mma.cta_group::2 - CTAs run as pairs
+//             (2-CTA clusters) on vertically adjacent tiles, one MMA covers 256 x BN, each SM
+//             stages only half of the B tile (6 stages of 32 KB at BN = 256)
+//   warp 2    TMEM allocator (2 accumulator stages: epilogue of tile i overlaps MMAs of tile i+1)
+//   warps 4-7 epilogue: tcgen05.ld (double buffered) -> bias / GeLU / ReLU from a shared-memory
+//             bias slice -> bf16 / fp32 -> swizzled 32 x 128 B boxes -> TMA tensor stores
+//             (reduce-add stores under split-K)
+// Tile order: bands of m-blocks sized so the band's A panel (~32 MB) stays in L2.
+// Split-K: when the tiles alone fill < 75 % of a wave (weight-gradient shapes).
+// Measured: 1.63 PFLOP/s at 8192^3 (cuBLAS 1.70), tensor pipe 94 % busy at the sustained clock;
+// history and ncu numbers in profiles/r1_gemm_2cta_analysis.md.
 //
 // Reference parity: the dense layers of the example trainers
-// (examples/v1/dist-mnist/dist_mnist.py:188-192 matmuls -> cuBLAS/Eigen in the
-// reference stack); BASELINE.json requires the GEMMs on the named paths to be
-// tcgen05/TMEM/TMA kernels rather than library calls.
+// (examples/v1/dist-mnist/dist_mnist.py:188-192 matmuls -> cuBLAS/Eigen in the reference stack);
+// BASELINE.json requires the GEMMs on the named paths to be tcgen05/TMEM/TMA kernels rather than
+// library calls.
 #include "common.cuh"
 #include "gemm_common.cuh"
 

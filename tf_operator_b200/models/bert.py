@@ -1,7 +1,9 @@
 """BERT encoder (base / large) for the TFJob Chief+Workers data-parallel pre-training config
-(BASELINE.json config 3). Every projection / MLP GEMM runs on the hand-written tcgen05 kernel
-(ops/gemm.TcLinear, bias and GeLU fused in the epilogue); attention uses torch's fused SDPA
-(a library op, like the convolutions in the ResNet path).
+(BASELINE.json config 3). Every projection / MLP / decoder GEMM - forward, dgrad and wgrad - runs
+on the hand-written tcgen05 kernel (ops/gemm); bias + residual + LayerNorm, bias + GeLU and the
+masked-LM cross-entropy are fused hand-written kernels (ops/layernorm, ops/xent); attention uses
+torch's fused SDPA (a library op, like the convolutions in the ResNet path). ``tc_gemm=False``
+builds the all-library twin (same parameters) that serves as the measured baseline.
 
 The reference has no BERT; the config is defined by BASELINE.json (bf16, seq 512, bucketed
 fused all-reduce).
