@@ -19,7 +19,11 @@ def main():
     ap.add_argument("--batch-size", type=int, default=256)
     ap.add_argument("--top", type=int, default=40)
     ap.add_argument("--out", default="")
+    ap.add_argument("--stem-bwd", default="", help="gather | scatter (ops.bn.STEM_BWD_MODE)")
     args = ap.parse_args()
+    if args.stem_bwd:
+        from tf_operator_b200.ops import bn as _bn
+        _bn.STEM_BWD_MODE = args.stem_bwd
     torch.manual_seed(0)
     B = args.batch_size
     eng = DataParallelEngine(ResNet(50), batch_size=B, image_size=224, lr=0.1, graph=False,
@@ -55,6 +59,9 @@ def main():
         print(f"  {t / total * 100:5.1f}%  {t / 1e3:8.3f} ms  {g}")
     for k, v in rows[:args.top]:
         print(f"  {v[0] / 1e3:9.3f} ms  x{v[1]:<4d} {k}")
+    for k, v in rows:
+        if "stem_bn" in k or "maxpool" in k:
+            print(f"  [stem tail] {v[0] / 1e3:9.3f} ms  x{v[1]:<4d} {k[:90]}")
     if args.out:
         json.dump({"total_kernel_ms": total / 1e3, "groups_ms": {g: t / 1e3 for g, t in groups.items()},
                    "kernels": [{"name": k, "ms": v[0] / 1e3, "calls": v[1]} for k, v in rows[:args.top]]},

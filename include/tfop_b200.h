@@ -141,6 +141,21 @@ int tfop_bn_bwd_apply(const void* dy, const void* x, const void* mask, const flo
                       const float* coef, void* dx, void* dres, size_t M, int C,
                       cudaStream_t stream);
 
+/* Stem tail fused (csrc/bn.cu): y = maxpool3x3/2/pad1(relu(bn(x))) without materialising the BN
+ * output; forward takes scale_shift from tfop_bn_fwd_stats, backward gathers the pooled gradient
+ * through the argmax codes inside both BN backward passes. NHWC bf16, C % 64 == 0. No reference
+ * counterpart (the reference ships no kernels). */
+int tfop_stem_bn_relu_pool_fwd(const void* x, const float* scale_shift, void* y, void* idx, int N,
+                               int H, int W, int C, cudaStream_t stream);
+int tfop_stem_bn_pool_bwd_reduce(const void* dpool, const void* idx, const void* x,
+                                 const float* save_mean, const float* save_invstd, int N, int H,
+                                 int W, int C, void* dgamma, void* dbeta, int param_dtype,
+                                 float* coef, void* workspace, cudaStream_t stream);
+int tfop_stem_bn_pool_bwd_apply(const void* dpool, const void* idx, const void* x,
+                                const float* save_mean, const float* save_invstd,
+                                const void* gamma, int param_dtype, const float* coef, void* dx,
+                                int N, int H, int W, int C, cudaStream_t stream);
+
 /* ---- MaxPool 3x3/2 pad 1, NHWC bf16 (csrc/pool.cu) -----------------------
  * No reference counterpart; ResNet stem pool. idx: 1 byte per output element. */
 int tfop_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C,

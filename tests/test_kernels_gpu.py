@@ -299,3 +299,51 @@ def test_hist_build_matches_index_add(dev, rows, feats):
     ref2 = build_histogram(bins.cpu(), g.cpu(), h.cpu(), idx.cpu())
     got2 = build_histogram(bins, g, h, idx)
     torch.testing.assert_close(got2.cpu(), ref2, rtol=1e-3, atol=1e-3)
+
+
+# ----------------------------------------------------------------------------- fused stem tail
+@pytest.mark.parametrize("shape", [(4, 64, 112, 112), (3, 64, 17, 23), (2, 128, 32, 32)])
+@pytest.mark.parametrize("bwd_mode", ["scatter", "gather"])
+def test_bn_relu_maxpool_fused_matches_separate_ops(dev, shape, bwd_mode, monkeypatch):
+    """maxpool(relu(bn(x))) in one pass (BN output never materialised) against the fp32
+    composition of the same ops: output, dx, dgamma, dbeta and the running statistics."""
+    from tf_operator_b200.ops import bn as bn_ops
+    from tf_operator_b200.ops.bn import FusedBatchNorm2d, bn_relu_maxpool
+    monkeypatch.setattr(bn_ops, "STEM_BWD_MODE", bwd_mode)
+    torch.manual_seed(sum(shape))
+    n, c, h, w = shape
+    x = (torch.randn(shape, device=dev) * 1.5 + 0.3).bfloat16().contiguous(
+        memory_format=torch.channels_last).requires_grad_(True)
+    bn = FusedBatchNorm2d(c).to(dev).bfloat16()
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(c) + 0.5)
+        bn.bias.copy_(torch.randn(c) * 0.3)
+    y = bn_relu_maxpool(bn, x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+
+    xf = x.detach().float().requires_grad_(True)
+    g = bn.weight.detach().float().requires_grad_(True)
+    b = bn.bias.detach().float().requires_grad_(True)
+    rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
+    yr = F.max_pool2d(F.relu(F.batch_norm(xf, rm, rv, g, b, True, 0.1, 1e-5)), 3, 2, 1)
+    yr.backward(dy.float())
+    assert y.shape == yr.shape
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=2e-2)
+    # a near-tie between two taps may pick a different argmax in bf16: compare in aggregate
+    err = (x.grad.float() - xf.grad).abs()
+    assert float(err.mean()) < 2e-3 and float((err > 0.05).float().mean()) < 2e-3
+    m = n * h * w
+    torch.testing.assert_close(bn.weight.grad.float(), g.grad, rtol=3e-2, atol=0.03 * m ** 0.5)
+    torch.testing.assert_close(bn.bias.grad.float(), b.grad, rtol=3e-2, atol=0.03 * m ** 0.5)
+    torch.testing.assert_close(bn.running_mean, rm, rtol=1e-2, atol=1e-3)
+    torch.testing.assert_close(bn.running_var, rv, rtol=1e-2, atol=1e-3)
+    # all-negative input: every window is dead, no gradient flows
+    bn2 = FusedBatchNorm2d(c).to(dev).bfloat16()
+    with torch.no_grad():
+        bn2.weight.fill_(0.0)
+        bn2.bias.fill_(-1.0)
+    x2 = torch.randn(shape, device=dev).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y2 = bn_relu_maxpool(bn2, x2)
+    y2.backward(torch.ones_like(y2))
+    assert float(y2.abs().max()) == 0.0 and float(x2.grad.abs().max()) == 0.0

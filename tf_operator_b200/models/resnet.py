@@ -12,7 +12,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from ..ops.bn import FusedBatchNorm2d
+from ..ops.bn import FusedBatchNorm2d, bn_relu_maxpool
 from ..ops.pool import MaxPool3x3s2
 from ..ops.conv_stem import stem_conv_s2d
 from ..ops.preproc import stem_weight_s2d
@@ -90,12 +90,15 @@ _CFG = {
 
 class ResNet(nn.Module):
     def __init__(self, depth: int = 50, num_classes: int = 1000, fused: bool = True,
-                 zero_init_residual: bool = True, width: int = 64):
+                 zero_init_residual: bool = True, width: int = 64, fused_stem_tail: bool = False):
         super().__init__()
         block, layers = _CFG[depth]
         self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
         self.bn1 = _bn(width, True, fused)
         self.pool = MaxPool3x3s2() if fused else nn.MaxPool2d(3, stride=2, padding=1)
+        # opt-in: BN + ReLU + max-pool of the stem in one pass. Measured a wash (the pooling-type
+        # kernels are instruction-bound, not bandwidth-bound: 21.55 vs 21.52 ms per step), so off.
+        self.fused_stem_tail = fused and fused_stem_tail
         stages, cin = [], width
         for i, nblk in enumerate(layers):
             w = width * (2 ** i)
@@ -117,7 +120,11 @@ class ResNet(nn.Module):
             x = stem_conv_s2d(x, stem_weight_s2d(self.conv1.weight))
         else:
             x = self.conv1(x)
-        x = self.pool(self.bn1(x))
+        if self.fused_stem_tail:
+            # BN + ReLU + max-pool in one pass, BN output never written (ops/bn.bn_relu_maxpool)
+            x = bn_relu_maxpool(self.bn1, x)
+        else:
+            x = self.pool(self.bn1(x))
         x = self.blocks(x)
         x = F.adaptive_avg_pool2d(x, 1).flatten(1)
         return self.fc(x)

@@ -59,6 +59,14 @@ _SIGS = {
     "tfop_bn_bwd_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_int,
                                   c_void_p]),
+    "tfop_stem_bn_relu_pool_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                           c_int, c_void_p]),
+    "tfop_stem_bn_pool_bwd_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                             c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p,
+                                             c_void_p, c_void_p]),
+    "tfop_stem_bn_pool_bwd_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                            c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                            c_void_p]),
     "tfop_maxpool3x3s2_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                       c_void_p]),
     "tfop_maxpool3x3s2_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
