@@ -53,10 +53,10 @@ def pod_from_template(template: Dict[str, Any], namespace: str, job, controller_
     pod = {
         "apiVersion": "v1", "kind": "Pod",
         "metadata": {"name": tmd.get("name"), "namespace": namespace,
-                     "labels": copy.deepcopy(tmd.get("labels") or {}),
-                     "annotations": copy.deepcopy(tmd.get("annotations") or {}),
-                     "ownerReferences": [copy.deepcopy(controller_ref)] if controller_ref else []},
-        "spec": copy.deepcopy(template.get("spec") or {}),
+                     "labels": c.deepcopy(tmd.get("labels") or {}),
+                     "annotations": c.deepcopy(tmd.get("annotations") or {}),
+                     "ownerReferences": [c.deepcopy(controller_ref)] if controller_ref else []},
+        "spec": c.deepcopy(template.get("spec") or {}),
         "status": {"phase": c.POD_PENDING},
     }
     if not pod["metadata"]["annotations"]:
@@ -101,10 +101,10 @@ class RealServiceControl:
         self.store, self.recorder = store, recorder
 
     def create_services_with_controller_ref(self, namespace, service, job, controller_ref):
-        svc = copy.deepcopy(service)
+        svc = c.deepcopy(service)
         svc.setdefault("apiVersion", "v1")
         svc.setdefault("kind", "Service")
-        svc.setdefault("metadata", {})["ownerReferences"] = [copy.deepcopy(controller_ref)]
+        svc.setdefault("metadata", {})["ownerReferences"] = [c.deepcopy(controller_ref)]
         try:
             new = self.store.create("services", svc, namespace)
         except ApiError as e:
@@ -148,8 +148,8 @@ class FakePodControl:
                 raise RuntimeError("not creating pod, limit %d already reached" % self.create_limit)
             if self.err is not None:
                 raise self.err
-            self.templates.append(copy.deepcopy(template))
-            self.controller_refs.append(copy.deepcopy(controller_ref))
+            self.templates.append(c.deepcopy(template))
+            self.controller_refs.append(c.deepcopy(controller_ref))
         return pod_from_template(template, namespace, job, controller_ref)
 
     def delete_pod(self, namespace, name, job):
@@ -179,8 +179,8 @@ class FakeServiceControl:
         with self._lock:
             if self.err is not None:
                 raise self.err
-            self.services.append(copy.deepcopy(service))
-            self.controller_refs.append(copy.deepcopy(controller_ref))
+            self.services.append(c.deepcopy(service))
+            self.controller_refs.append(c.deepcopy(controller_ref))
         return service
 
     def delete_service(self, namespace, name, job):

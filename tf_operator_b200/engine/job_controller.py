@@ -170,11 +170,11 @@ class JobController:
 
     # ------------------------------------------------------------------ writes
     def update_job_status_in_api_server(self, job, status) -> None:
-        job["status"] = copy.deepcopy(status)
+        job["status"] = c.deepcopy(status)
         if self.store is None:
             return
         latest = self.store.get(self.info.plural, c.namespace_of(job), c.name_of(job))
-        latest["status"] = copy.deepcopy(status)
+        latest["status"] = c.deepcopy(status)
         self.store.update_status(self.info.plural, latest)
 
     def delete_job(self, job) -> None:
@@ -243,7 +243,7 @@ class JobController:
         labels[c.LABEL_REPLICA_INDEX] = index
         if master_role:
             labels[c.LABEL_JOB_ROLE] = "master"
-        template = copy.deepcopy(spec.get("template") or {})
+        template = c.deepcopy(spec.get("template") or {})
         tmd = template.setdefault("metadata", {})
         tmd["name"] = c.gen_general_name(c.name_of(job), rt, index)
         tlabels = tmd.setdefault("labels", {}) or {}
@@ -406,7 +406,7 @@ class JobController:
         if sp.get("priorityClass"):
             pg["spec"]["priorityClassName"] = sp["priorityClass"]
         if sp.get("minResources"):
-            pg["spec"]["minResources"] = copy.deepcopy(sp["minResources"])
+            pg["spec"]["minResources"] = c.deepcopy(sp["minResources"])
         return self.store.create("podgroups", pg, ns)
 
     def delete_pod_group(self, job) -> None:
@@ -424,7 +424,7 @@ class JobController:
         log.debug("Reconciling for job %s", job_key)
         pods = self.get_pods_for_job(job)
         services = self.get_services_for_job(job)
-        old_status = copy.deepcopy(status)
+        old_status = c.deepcopy(status)
 
         if c.is_finished(status):
             self.delete_pods_and_services(run_policy, job, pods)

@@ -33,7 +33,7 @@ class KindReconciler(JobController):
         self.module.set_defaults(job)
         status = c.status_of(job)
         msg = self.created_message.format(kind=self.info.kind, name=c.name_of(job))
-        before = copy.deepcopy(status)
+        before = c.deepcopy(status)
         c.update_job_conditions(status, c.JOB_CREATED, self.created_reason, msg)
         if self.metrics is not None and before != status:
             self.metrics.jobs_created.labels(c.namespace_of(job)).inc()

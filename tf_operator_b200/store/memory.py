@@ -151,7 +151,7 @@ class Watch:
             return
         if not fields_match(obj, self._fields):
             return
-        self._q.put((etype, copy.deepcopy(obj)))
+        self._q.put((etype, c.deepcopy(obj)))
 
     def stop(self):
         self._stopped = True
@@ -200,7 +200,7 @@ class ObjectStore:
                 w._offer(etype, obj)
         for fn in list(self._listeners):
             try:
-                fn(resource, etype, copy.deepcopy(obj))
+                fn(resource, etype, c.deepcopy(obj))
             except Exception:  # a listener must never break the store
                 import traceback
                 traceback.print_exc()
@@ -249,7 +249,7 @@ class ObjectStore:
 
     # ---- CRUD ---------------------------------------------------------------
     def create(self, resource: str, obj: Dict[str, Any], namespace: Optional[str] = None) -> Dict[str, Any]:
-        obj = copy.deepcopy(obj)
+        obj = c.deepcopy(obj)
         md = obj.setdefault("metadata", {})
         if not md.get("name"):
             if md.get("generateName"):
@@ -277,14 +277,14 @@ class ObjectStore:
             self._objs[key] = obj
             self.audit.append(("create", resource, ns, md["name"]))
             self._emit(resource, "ADDED", obj)
-            return copy.deepcopy(obj)
+            return c.deepcopy(obj)
 
     def get(self, resource: str, namespace: Optional[str], name: str) -> Dict[str, Any]:
         with self._lock:
             obj = self._objs.get((resource, self._ns(resource, namespace), name))
             if obj is None:
                 raise not_found(resource, name)
-            return copy.deepcopy(obj)
+            return c.deepcopy(obj)
 
     def list(self, resource: str, namespace: Optional[str] = None, label_selector=None,
              field_selector: Optional[str] = None) -> List[Dict[str, Any]]:
@@ -300,7 +300,7 @@ class ObjectStore:
                     continue
                 if not fields_match(obj, field_selector):
                     continue
-                out.append(copy.deepcopy(obj))
+                out.append(c.deepcopy(obj))
             out.sort(key=lambda o: (c.namespace_of(o), c.name_of(o)))
             return out
 
@@ -319,13 +319,13 @@ class ObjectStore:
             rv = md.get("resourceVersion")
             if rv and rv != cur["metadata"]["resourceVersion"]:
                 raise conflict(resource, name)
-            new = copy.deepcopy(obj)
+            new = c.deepcopy(obj)
             if status_only:
-                merged = copy.deepcopy(cur)
+                merged = c.deepcopy(cur)
                 merged["status"] = new.get("status", {})
                 new = merged
             elif spec_only and resource in STATUS_SUBRESOURCE:
-                new["status"] = copy.deepcopy(cur.get("status", {}))
+                new["status"] = c.deepcopy(cur.get("status", {}))
             if resource in JOB_RESOURCES and self.admission_enabled and not status_only:
                 self._admit_job(resource, new)
             nmd = new.setdefault("metadata", {})
@@ -342,7 +342,7 @@ class ObjectStore:
             self._objs[key] = new
             self.audit.append(("update_status" if status_only else "update", resource, ns, name))
             self._emit(resource, "MODIFIED", new)
-            return copy.deepcopy(new)
+            return c.deepcopy(new)
 
     def update(self, resource: str, obj: Dict[str, Any]) -> Dict[str, Any]:
         return self._write(resource, obj, status_only=False, spec_only=True)
@@ -381,7 +381,7 @@ class ObjectStore:
             obj["metadata"].setdefault("deletionTimestamp", c.now_rfc3339())
             self.audit.append(("delete", resource, key[1], name))
             self._emit(resource, "DELETED", obj)
-            return copy.deepcopy(obj)
+            return c.deepcopy(obj)
 
     def watch(self, resource: str, namespace: Optional[str] = None, label_selector=None,
               field_selector: Optional[str] = None, send_initial: bool = True) -> Watch:
@@ -413,7 +413,7 @@ class ObjectStore:
 
 def _merge_patch(target, patch):
     if not isinstance(patch, dict):
-        return copy.deepcopy(patch)
+        return c.deepcopy(patch)
     if not isinstance(target, dict):
         target = {}
     out = dict(target)
