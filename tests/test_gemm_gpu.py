@@ -322,4 +322,4 @@ def test_gemm_split_k_heuristic_picks_splits_only_for_small_outputs(gemm_ok):
     finally:
         lib.tfop_gemm_set_splits(0)
     torch.testing.assert_close(auto.float(), never.float(), rtol=3e-2, atol=3.0)
-    assert t_auto < t_never * 0.9, (t_auto, t_never)
+    assert t_auto < t_never * 0.97, (t_auto, t_never)   # measured ratio 0.74; loose on purpose
