@@ -15,6 +15,7 @@ import torch.nn.functional as F
 from ..ops.bn import FusedBatchNorm2d, bn_relu_maxpool
 from ..ops.pool import MaxPool3x3s2
 from ..ops.conv_stem import stem_conv_s2d
+from ..ops.gemm import TcLinear
 from ..ops.preproc import stem_weight_s2d
 
 
@@ -107,7 +108,8 @@ class ResNet(nn.Module):
                                     zero_init_residual))
                 cin = w * block.expansion
         self.blocks = nn.Sequential(*stages)
-        self.fc = nn.Linear(cin, num_classes)
+        # classifier GEMM (forward, dgrad, wgrad) on the tcgen05 kernel; plain nn.Linear off-GPU
+        self.fc = TcLinear(cin, num_classes) if fused else nn.Linear(cin, num_classes)
         for m in self.modules():
             if isinstance(m, nn.Conv2d):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
