@@ -48,7 +48,10 @@ def main():
     groups = defaultdict(float)
     for k, v in rows:
         lk = k.lower()
-        g = ("gemm / conv-stem (ours)" if "conv_stem" in lk else "conv (cuDNN/cutlass)" if any(t in lk for t in ("implicit_gemm", "cudnn", "xmma", "conv", "nchwtonhwc", "nhwctonchw"))
+        g = ("gemm / conv-stem (ours)" if "conv_stem" in lk
+             else "conv fwd+dgrad tcgen05 (ours)" if "conv_igemm" in lk
+             else "conv wgrad tcgen05 (ours)" if "conv_wgrad" in lk
+             else "conv (cuDNN/cutlass)" if any(t in lk for t in ("implicit_gemm", "cudnn", "xmma", "conv", "nchwtonhwc", "nhwctonchw"))
              else "bn (ours)" if "bn_" in lk else "pool (ours)" if "pool" in lk
              else "optimizer/pack (ours)" if any(t in lk for t in ("sgd", "pack", "adamw")) else
              "gemm / conv-stem (ours)" if ("gemm_tn" in lk or "conv_stem" in lk) else "preproc (ours)" if ("stem" in lk or "u8" in lk)

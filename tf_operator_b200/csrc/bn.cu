@@ -138,6 +138,39 @@ __global__ void __launch_bounds__(kT, 4) bn_fwd_stats_kernel(
     if (threadIdx.x == 0) counters[blockIdx.y] = 0u;
 }
 
+// Statistics from sums the producer already reduced: the convolution epilogue (conv_tc.cu) adds
+// the per-channel sum and sum of squares of its output to sums[2][C]; this turns them into
+// mean / invstd / scale_shift / running statistics and clears the sums for the next step, so the
+// read of the convolution output that bn_fwd_stats_kernel makes never happens.
+__global__ void __launch_bounds__(256) bn_finalize_kernel(
+    float* __restrict__ sums, size_t M, int C, const void* __restrict__ gamma,
+    const void* __restrict__ beta, int param_dtype, float* __restrict__ running_mean,
+    float* __restrict__ running_var, float momentum, float eps, float* __restrict__ scale_shift,
+    float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float S = sums[c], Q = sums[C + c];
+    sums[c] = 0.f;
+    sums[C + c] = 0.f;
+    const float invM = 1.f / (float)M;
+    const float mean = S * invM;
+    float var = fmaf(-mean, mean, Q * invM);
+    var = fmaxf(var, 0.f);
+    const float invstd = rsqrtf(var + eps);
+    const float g = ld_param(gamma, param_dtype, c);
+    const float bt = ld_param(beta, param_dtype, c);
+    const float a = g * invstd;
+    scale_shift[c] = a;
+    scale_shift[C + c] = fmaf(-mean, a, bt);
+    save_mean[c] = mean;
+    save_invstd[c] = invstd;
+    if (running_mean) {
+        const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    }
+}
+
 template <bool RELU, bool RES>
 __global__ void __launch_bounds__(kT, 4) bn_fwd_apply_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
@@ -530,6 +563,22 @@ TFOP_API int tfop_bn_fwd_stats(const void* x, size_t M, int C, const void* gamma
         (const __nv_bfloat16*)x, M, C, (float*)workspace, ws_counter(workspace), gamma, beta,
         param_dtype, running_mean, running_var, momentum, eps, scale_shift, save_mean,
         save_invstd);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Same outputs as tfop_bn_fwd_stats, from sums[2][C] (fp32: per-channel sum and sum of squares
+// over the M rows) that the producing convolution accumulated (tfop_conv_fwd `stats`). Clears
+// `sums` so the array can be handed to the next step's convolution as it is.
+TFOP_API int tfop_bn_finalize(float* sums, size_t M, int C, const void* gamma, const void* beta,
+                              int param_dtype, float* running_mean, float* running_var,
+                              float momentum, float eps, float* scale_shift, float* save_mean,
+                              float* save_invstd, cudaStream_t stream) {
+    TFOP_REQUIRE(sums != nullptr && M > 0 && C > 0, "bn_finalize: bad arguments");
+    bn_finalize_kernel<<<(C + 255) / 256, 256, 0, stream>>>(sums, M, C, gamma, beta, param_dtype,
+                                                            running_mean, running_var, momentum,
+                                                            eps, scale_shift, save_mean,
+                                                            save_invstd);
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }

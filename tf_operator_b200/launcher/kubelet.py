@@ -54,6 +54,11 @@ class KubeletOptions:
     extra_env: Dict[str, str] = field(default_factory=dict)
     python: str = sys.executable
     cwd: str = ""
+    # local "image registry": image name -> directory standing in for the image's root file
+    # system. Absolute paths in command / args / `--flag=/path` whose first component exists
+    # under that directory are rewritten into it, so a manifest written for a container image
+    # (`python /var/tf_mnist/mnist_with_summaries.py --log_dir=/train/logs`) runs unchanged.
+    image_roots: Dict[str, str] = field(default_factory=dict)
 
 
 class _Container:
@@ -224,7 +229,21 @@ class LocalKubelet:
                              f"(images are not pulled by the local launcher)")
         if cmd[0] in ("python", "python3"):
             cmd[0] = self.opt.python
+        root = self.opt.image_roots.get(ctr.get("image") or "")
+        if root:
+            cmd = [cmd[0]] + [self._into_image_root(str(a), root) for a in cmd[1:]]
         return [str(x) for x in cmd]
+
+    @staticmethod
+    def _into_image_root(arg: str, root: str) -> str:
+        head, sep, tail = arg.partition("=")
+        path, prefix = (tail, head + sep) if (sep and tail.startswith("/")) else (arg, "")
+        if not path.startswith("/"):
+            return arg
+        first = path.lstrip("/").split("/", 1)[0]
+        if first and (Path(root) / first).exists():
+            return prefix + str(Path(root) / path.lstrip("/"))
+        return arg
 
     def _env_for(self, rt: _PodRuntime, pod, ctr) -> Dict[str, str]:
         env = dict(os.environ)

@@ -1,8 +1,10 @@
 """ResNet family (18/34/50/101/152) for the PyTorchJob ResNet-50 DDP config
-(BASELINE.json config 2). Convolutions are cuDNN (a plain library op); every
-BatchNorm+ReLU(+residual add) goes through the fused NHWC kernels in
-ops/bn.py. ``fused=False`` builds the same network from stock torch modules and
-is the "reference mode" compute graph for the measured NCCL baseline
+(BASELINE.json config 2). Every convolution runs on the hand-written tcgen05 implicit-GEMM
+kernels (ops/conv.py for the 1x1 / 3x3 layers, ops/conv_stem.py for the stem); their epilogues
+also reduce the BatchNorm statistics, and their data gradients are added into the shortcut
+branch's gradient inside the kernel. Every BatchNorm+ReLU(+residual add) goes through the fused
+NHWC kernels in ops/bn.py. ``fused=False`` builds the same network from stock torch modules
+(cuDNN convolutions) and is the "reference mode" compute graph for the measured NCCL baseline
 (BASELINE.md section 3). The reference itself has no model code; its CNN example is
 examples/v1/distribution_strategy/keras-API/multi_worker_strategy-with-keras.py:42-60.
 """
@@ -14,6 +16,7 @@ import torch.nn.functional as F
 
 from ..ops.bn import FusedBatchNorm2d, bn_relu_maxpool
 from ..ops.pool import MaxPool3x3s2
+from ..ops.conv import TcConv2d, conv2d_pair, conv2d_skip
 from ..ops.conv_stem import stem_conv_s2d
 from ..ops.gemm import TcLinear
 from ..ops.preproc import stem_weight_s2d
@@ -39,47 +42,82 @@ def _bn(c, relu=True, fused=True, zero_init=False):
         else _StockBNAct(c, relu, zero_init)
 
 
-def _conv(cin, cout, k, stride=1):
+def _conv(cin, cout, k, stride=1, fused=True):
+    # the tcgen05 kernels tile channels in 64s; other widths (toy models of the CPU tests) are
+    # built from the stock module, decided here at construction, never per call
+    if fused and cin % 64 == 0 and cout % 64 == 0:
+        return TcConv2d(cin, cout, k, stride)
     return nn.Conv2d(cin, cout, k, stride=stride, padding=k // 2, bias=False)
 
 
-class Bottleneck(nn.Module):
+class _Block(nn.Module):
+    """Shared forward of the residual blocks. On the native path the first convolution and the
+    shortcut are issued together (conv2d_skip / conv2d_pair), so their data gradients meet inside
+    the dgrad kernel, and each convolution hands its BatchNorm the statistics it reduced."""
+
+    def _native(self):
+        return isinstance(self.conv1, TcConv2d) and (
+            self.down is None or isinstance(self.down[0], TcConv2d))
+
+    def _head(self, x):
+        """(bn1(conv1(x)), shortcut)"""
+        if not self._native():
+            idt = x if self.down is None else self.down[1](self.down[0](x))
+            return self.bn1(self.conv1(x)), idt
+        tr = self.training
+        st1 = self.conv1.sums(x) if tr else None
+        if self.down is None:
+            y, idt = conv2d_skip(x, self.conv1.weight, self.conv1.stride, st1)
+        else:
+            dconv, dbn = self.down
+            std = dconv.sums(x) if tr else None
+            y, d = conv2d_pair(x, self.conv1.weight, self.conv1.stride, st1,
+                               dconv.weight, dconv.stride, std)
+            idt = dbn(d, sums=std)
+        return self.bn1(y, sums=st1), idt
+
+    def _conv_bn(self, conv, bn, x, residual=None):
+        if isinstance(conv, TcConv2d):
+            st = conv.sums(x) if self.training else None
+            return bn(conv(x, st), residual, sums=st)
+        return bn(conv(x), residual)
+
+
+class Bottleneck(_Block):
     expansion = 4
 
     def __init__(self, cin, width, stride, fused, zero_init_residual):
         super().__init__()
         cout = width * self.expansion
-        self.conv1, self.bn1 = _conv(cin, width, 1), _bn(width, True, fused)
-        self.conv2, self.bn2 = _conv(width, width, 3, stride), _bn(width, True, fused)
-        self.conv3 = _conv(width, cout, 1)
+        self.conv1, self.bn1 = _conv(cin, width, 1, 1, fused), _bn(width, True, fused)
+        self.conv2, self.bn2 = _conv(width, width, 3, stride, fused), _bn(width, True, fused)
+        self.conv3 = _conv(width, cout, 1, 1, fused)
         self.bn3 = _bn(cout, True, fused, zero_init=zero_init_residual)
         self.down = None
         if stride != 1 or cin != cout:
-            self.down = nn.ModuleList([_conv(cin, cout, 1, stride), _bn(cout, False, fused)])
+            self.down = nn.ModuleList([_conv(cin, cout, 1, stride, fused), _bn(cout, False, fused)])
 
     def forward(self, x):
-        idt = x if self.down is None else self.down[1](self.down[0](x))
-        y = self.bn1(self.conv1(x))
-        y = self.bn2(self.conv2(y))
-        return self.bn3(self.conv3(y), idt)
+        y, idt = self._head(x)
+        y = self._conv_bn(self.conv2, self.bn2, y)
+        return self._conv_bn(self.conv3, self.bn3, y, idt)
 
 
-class BasicBlock(nn.Module):
+class BasicBlock(_Block):
     expansion = 1
 
     def __init__(self, cin, width, stride, fused, zero_init_residual):
         super().__init__()
-        self.conv1, self.bn1 = _conv(cin, width, 3, stride), _bn(width, True, fused)
-        self.conv2 = _conv(width, width, 3)
+        self.conv1, self.bn1 = _conv(cin, width, 3, stride, fused), _bn(width, True, fused)
+        self.conv2 = _conv(width, width, 3, 1, fused)
         self.bn2 = _bn(width, True, fused, zero_init=zero_init_residual)
         self.down = None
         if stride != 1 or cin != width:
-            self.down = nn.ModuleList([_conv(cin, width, 1, stride), _bn(width, False, fused)])
+            self.down = nn.ModuleList([_conv(cin, width, 1, stride, fused), _bn(width, False, fused)])
 
     def forward(self, x):
-        idt = x if self.down is None else self.down[1](self.down[0](x))
-        y = self.bn1(self.conv1(x))
-        return self.bn2(self.conv2(y), idt)
+        y, idt = self._head(x)
+        return self._conv_bn(self.conv2, self.bn2, y, idt)
 
 
 _CFG = {
@@ -111,7 +149,7 @@ class ResNet(nn.Module):
         # classifier GEMM (forward, dgrad, wgrad) on the tcgen05 kernel; plain nn.Linear off-GPU
         self.fc = TcLinear(cin, num_classes) if fused else nn.Linear(cin, num_classes)
         for m in self.modules():
-            if isinstance(m, nn.Conv2d):
+            if isinstance(m, (nn.Conv2d, TcConv2d)):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
 
     def forward(self, x):

@@ -51,6 +51,9 @@ _SIGS = {
     "tfop_bn_fwd_stats": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p, c_int, c_void_p,
                                   c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p]),
+    "tfop_bn_finalize": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p, c_int, c_void_p,
+                                 c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p,
+                                 c_void_p]),
     "tfop_bn_fwd_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                   c_int, c_int, c_void_p]),
     "tfop_bn_bwd_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
@@ -116,6 +119,10 @@ _SIGS = {
     "tfop_conv_stem_s2d_wgrad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "tfop_conv_stem_set_mode": (c_int, [c_int]),
     "tfop_conv_stem_s2d_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "tfop_conv_fwd": (c_int, [c_void_p] * 4 + [c_int] * 7 + [c_void_p]),
+    "tfop_conv_dgrad": (c_int, [c_void_p] * 3 + [c_int] * 8 + [c_void_p]),
+    "tfop_conv_wgrad": (c_int, [c_void_p] * 3 + [c_int] * 7 + [c_void_p]),
+    "tfop_conv_set_cluster_mode": (c_int, [c_int]),
     "tfop_transpose_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
@@ -161,8 +168,10 @@ def load():
         for name, (res, args) in {**_SIGS, **EXTRA_SIGS}.items():
             try:
                 fn = getattr(lib, name)
-            except AttributeError:
-                continue
+            except AttributeError as e:
+                raise TfopError(f"{path} lacks the entry point {name}: the library is older "
+                                f"than the Python package; rebuild it with "
+                                f"`python -m tf_operator_b200.ops._build --force`") from e
             fn.restype = res
             fn.argtypes = args
         _lib = lib

@@ -39,7 +39,7 @@ def supported(x: torch.Tensor) -> bool:
 class _FusedBNAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, res, gamma, beta, running_mean, running_var, training, momentum, eps,
-                relu):
+                relu, sums=None):
         lib = _lib.load()
         if not _is_nhwc(x):
             x = x.contiguous(memory_format=torch.channels_last)
@@ -54,11 +54,19 @@ class _FusedBNAct(torch.autograd.Function):
         if training:
             save_mean = torch.empty(c, dtype=torch.float32, device=dev)
             save_invstd = torch.empty(c, dtype=torch.float32, device=dev)
-            _lib.check(lib.tfop_bn_fwd_stats(
-                x.data_ptr(), m, c, gamma.data_ptr(), beta.data_ptr(), pd,
-                _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps),
-                scale_shift.data_ptr(), save_mean.data_ptr(), save_invstd.data_ptr(),
-                _workspace(dev).data_ptr(), st), "bn_fwd_stats")
+            if sums is not None:
+                # the producing convolution's epilogue already reduced sum / sum of squares
+                _lib.check(lib.tfop_bn_finalize(
+                    sums.data_ptr(), m, c, gamma.data_ptr(), beta.data_ptr(), pd,
+                    _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps),
+                    scale_shift.data_ptr(), save_mean.data_ptr(), save_invstd.data_ptr(), st),
+                    "bn_finalize")
+            else:
+                _lib.check(lib.tfop_bn_fwd_stats(
+                    x.data_ptr(), m, c, gamma.data_ptr(), beta.data_ptr(), pd,
+                    _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps),
+                    scale_shift.data_ptr(), save_mean.data_ptr(), save_invstd.data_ptr(),
+                    _workspace(dev).data_ptr(), st), "bn_fwd_stats")
         else:
             invstd = torch.rsqrt(running_var.float() + eps)
             a = gamma.float() * invstd
@@ -110,15 +118,17 @@ class _FusedBNAct(torch.autograd.Function):
             _lib.ptr(dres), m, c, st), "bn_bwd_apply")
         if ctx.has_res and dres is None:
             dres = dy
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
 
 
 def fused_bn_act(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5,
-                 relu=True, residual=None):
-    """y = [relu](batch_norm(x) [+ residual]); CUDA bf16 NHWC uses the fused kernels."""
+                 relu=True, residual=None, sums=None):
+    """y = [relu](batch_norm(x) [+ residual]); CUDA bf16 NHWC uses the fused kernels. ``sums``:
+    the [2, C] fp32 sum / sum-of-squares array the producing convolution filled (ops/conv.py);
+    it replaces the statistics pass over x and is cleared for the next step."""
     if supported(x):
         return _FusedBNAct.apply(x, residual, gamma, beta, running_mean, running_var, training,
-                                 momentum, eps, relu)
+                                 momentum, eps, relu, sums if training else None)
     # CPU tensors, or a channel count the kernels do not cover (not a multiple of 64)
     y = F.batch_norm(x, running_mean, running_var, gamma, beta, training, momentum, eps)
     if residual is not None:
@@ -228,10 +238,10 @@ class FusedBatchNorm2d(nn.Module):
         self.register_buffer("running_mean", torch.zeros(num_features, dtype=torch.float32))
         self.register_buffer("running_var", torch.ones(num_features, dtype=torch.float32))
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, sums=None):
         if self.running_mean.dtype != torch.float32:
             # a blanket .to(bfloat16) also casts buffers; statistics stay fp32
             self.running_mean = self.running_mean.float()
             self.running_var = self.running_var.float()
         return fused_bn_act(x, self.weight, self.bias, self.running_mean, self.running_var,
-                            self.training, self.momentum, self.eps, self.relu, residual)
+                            self.training, self.momentum, self.eps, self.relu, residual, sums)
