@@ -103,9 +103,10 @@ def _schema_rows(schema: dict, prefix: str, rows: list, depth: int = 0) -> None:
 def api_page() -> str:
     out = ["# API reference: kubeflow.org/v1", "",
            "Generated from the CRD schemas (`python -m tf_operator_b200.api.crd`); the pod template "
-           "is free-form (`x-kubernetes-preserve-unknown-fields`) exactly as in the reference CRDs.", ""]
+           "is the full structural core/v1 PodTemplateSpec, as in the reference CRDs (not expanded "
+           "here).", ""]
     for kind, mod in KINDS.items():
-        schema = crd_for(mod)["spec"]["versions"][0]["schema"]["openAPIV3Schema"]
+        schema = crd_for(mod, full=False)["spec"]["versions"][0]["schema"]["openAPIV3Schema"]
         out += [f"## {kind}", "", f"Resource `{mod.INFO.plural}.kubeflow.org`, singular `{mod.INFO.singular}`.", "",
                 "| field | type | required | description |", "|---|---|---|---|"]
         rows: list = []

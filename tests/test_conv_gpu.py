@@ -113,7 +113,7 @@ def test_conv_weight_gradient(cfg):
 def test_conv_cta_pairing_modes_agree(mode):
     """cta_group::2 pairs and single CTAs compute the same tiles (bitwise: same MMA order)."""
     from tf_operator_b200.ops import _lib
-    from tf_operator_b200.ops.conv import conv_fwd, conv_dgrad
+    from tf_operator_b200.ops.conv import conv_fwd, conv_dgrad, conv_wgrad
     lib = _lib.load()
     x, w = _mk(8, 28, 128, 256, 3, seed=3)
     try:
@@ -121,12 +121,16 @@ def test_conv_cta_pairing_modes_agree(mode):
         y0 = conv_fwd(x, w, 1)
         dy = torch.randn_like(y0)
         d0 = conv_dgrad(dy, w, x.shape, 1)
+        g0 = conv_wgrad(x, dy, w.float(), 1)
         _lib.check(lib.tfop_conv_set_cluster_mode(mode))
         y1 = conv_fwd(x, w, 1)
         d1 = conv_dgrad(dy, w, x.shape, 1)
+        g1 = conv_wgrad(x, dy, w.float(), 1)
     finally:
         _lib.check(lib.tfop_conv_set_cluster_mode(-1))
     assert torch.equal(y0, y1) and torch.equal(d0, d1)
+    # the weight gradient sums fp32 partial tiles in whatever order they arrive
+    torch.testing.assert_close(g0, g1, rtol=1e-4, atol=1e-3)
 
 
 def test_conv_autograd_functions_match_torch():

@@ -167,3 +167,85 @@ def test_active_deadline_fires_without_any_other_event():
         assert store.list("pods") == []
     finally:
         m.stop()
+
+
+def test_pprof_endpoints_and_sync_duration_log(caplog):
+    """The monitoring port serves the net/http/pprof set (cmd/tf-operator.v1/main.go:21,39-50)
+    and every sync logs its wall time (controller.go:303-307 "Finished syncing tfjob %q (%v)")."""
+    import logging
+    store = ObjectStore()
+    m = Manager(store, ManagerOptions(metrics_bind_address="127.0.0.1:0",
+                                      health_probe_bind_address="127.0.0.1:0")).start()
+    try:
+        mport = m._servers[0].server_address[1]
+
+        def get(path):
+            return urllib.request.urlopen(f"http://127.0.0.1:{mport}{path}").read().decode()
+        idx = get("/debug/pprof/")
+        for name in ("goroutine", "heap", "profile", "threadcreate", "cmdline"):
+            assert name in idx
+        assert "TFJob-worker-0" in get("/debug/pprof/goroutine?debug=2")
+        prof = get("/debug/pprof/profile?seconds=0.3")
+        assert "_worker (manager.py:" in prof and prof.strip().split()[-1].isdigit()
+        assert "tracemalloc" in get("/debug/pprof/heap") or "traced current" in get("/debug/pprof/heap")
+        assert "traced current" in get("/debug/pprof/heap")
+        assert "resync\tdaemon=True" in get("/debug/pprof/threadcreate")
+        assert get("/debug/pprof/cmdline")
+        with caplog.at_level(logging.INFO, logger="tf_operator_b200.operator"):
+            store.create("tfjobs", _tfjob("sync-log"))
+            assert m.wait_idle()
+        msgs = [r.getMessage() for r in caplog.records if "Finished syncing" in r.getMessage()]
+        assert msgs and "Finished syncing tfjob 'default/sync-log' (" in msgs[0] and msgs[0].endswith("ms)")
+        text = get("/metrics")
+        assert 'training_operator_reconcile_seconds_count{kind="TFJob"}' in text
+    finally:
+        m.stop()
+        import tracemalloc
+        tracemalloc.stop()
+
+
+def test_two_workers_never_mix_up_the_pods_of_concurrent_tfjobs():
+    """the TFJob reconciler is shared by `threadiness` worker threads; the pod list it
+    remembers between reconcile_pods() and update_job_status() must be the calling thread's own.
+    Job a's worker-0 has succeeded, job b's is still running: with the syncs of a and b forced to
+    interleave, b must not be marked Succeeded on the strength of a's pods."""
+    from tf_operator_b200.kinds.tf import TFJobReconciler
+    store = ObjectStore()
+    m = Manager(store, ManagerOptions(threadiness=2, enabled_schemes=["TFJob"],
+                                      metrics_bind_address="", health_probe_bind_address="")).start()
+    gate = threading.Barrier(2, timeout=2)
+    orig = TFJobReconciler.update_job_status
+    seen = []
+
+    def slow_update(self, job, replicas, status):
+        seen.append((threading.current_thread().name, c.name_of(job)))
+        try:
+            gate.wait()        # both threads have stored their pod lists before either reads one
+        except threading.BrokenBarrierError:
+            pass
+        return orig(self, job, replicas, status)
+
+    try:
+        for name in ("a", "b"):
+            job = _tfjob(name)
+            job["spec"]["tfReplicaSpecs"]["Worker"]["replicas"] = 2
+            store.create("tfjobs", job)
+        assert m.wait_idle()
+        TFJobReconciler.update_job_status = slow_update
+        for p in store.list("pods"):
+            done = p["metadata"]["name"] == "a-worker-0"
+            p["status"] = {"phase": "Succeeded" if done else "Running", "containerStatuses": [
+                {"name": "tensorflow",
+                 "state": {"terminated": {"exitCode": 0}} if done else {"running": {}}}]}
+            store.update_status("pods", p)
+        assert m.wait_idle(timeout=15)
+        time.sleep(0.3)
+        assert m.wait_idle(timeout=15)
+    finally:
+        TFJobReconciler.update_job_status = orig
+        m.stop()
+    assert len({t for t, _ in seen}) == 2, seen        # both worker threads took part
+    conds = {n: [cd["type"] for cd in store.get("tfjobs", "default", n)["status"]["conditions"]]
+             for n in ("a", "b")}
+    assert "Succeeded" in conds["a"], conds
+    assert "Succeeded" not in conds["b"] and "Running" in conds["b"], conds

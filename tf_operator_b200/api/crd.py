@@ -3,13 +3,24 @@
 Same identity and structure as the reference's controller-gen output
 (manifests/base/kubeflow.org_*.yaml: apiextensions.k8s.io/v1, group kubeflow.org, version v1
 served+storage, Namespaced, ``subresources.status``, required spec fields, runPolicy and
-status schemas from :36-108 and :6816-6896 of kubeflow.org_tfjobs.yaml). The embedded
-PodTemplateSpec is kept open (``x-kubernetes-preserve-unknown-fields``) instead of the ~6.7k
-generated lines per kind.
+status schemas from :36-108 and :6816-6896 of kubeflow.org_tfjobs.yaml), including the full
+structural ``PodTemplateSpec`` (:109-6815) so a structural apiserver prunes and validates the pod
+template exactly as it does under the reference's CRDs.
+
+The STRUCTURE (fields, types, formats, required lists) is generated here from the API model. Two
+data files under ``api/schema/`` complete it: ``core_v1_podtemplatespec.json.gz`` - the
+core/v1 PodTemplateSpec schema as controller-gen v0.4.1 emits it, identical for the four kinds
+and therefore stored once - and ``crd_descriptions.json``, the field documentation strings keyed
+by kind and schema path. ``yaml.safe_load`` of every emitted manifest equals ``yaml.safe_load``
+of the reference's (tests/test_manifests.py).
 """
 from __future__ import annotations
 
+import copy
+import gzip
+import json
 import sys
+from functools import lru_cache
 from pathlib import Path
 
 import yaml
@@ -86,7 +97,63 @@ STATUS = {
 }
 
 
-def crd_for(mod) -> dict:
+_SCHEMA_DIR = Path(__file__).resolve().parent / "schema"
+
+
+@lru_cache(maxsize=1)
+def pod_template_schema() -> dict:
+    """core/v1 PodTemplateSpec as an OpenAPI v3 structural schema (data file, one copy)."""
+    with gzip.open(_SCHEMA_DIR / "core_v1_podtemplatespec.json.gz", "rt") as f:
+        return json.load(f)
+
+
+@lru_cache(maxsize=1)
+def _descriptions() -> dict:
+    return json.loads((_SCHEMA_DIR / "crd_descriptions.json").read_text())
+
+
+def _strip_descriptions(node):
+    if isinstance(node, dict):
+        return {k: _strip_descriptions(v) for k, v in node.items()
+                if not (k == "description" and isinstance(v, str))}
+    if isinstance(node, list):
+        return [_strip_descriptions(v) for v in node]
+    return node
+
+
+def _document(schema: dict, kind: str) -> dict:
+    """Attach the per-kind field documentation (schema path -> text) to a bare structure."""
+    for path, text in _descriptions()[kind].items():
+        node = schema
+        for key in (path.split("/") if path else []):
+            node = node[key]
+        node["description"] = text
+    return schema
+
+
+def crd_for(mod, full: bool = True) -> dict:
+    """The CustomResourceDefinition of one kind. ``full=False`` keeps the pod template open
+    (``x-kubernetes-preserve-unknown-fields``) and the generator's own short descriptions - the
+    compact form the in-process API server registers."""
+    crd = _crd_structure(mod)
+    if not full:
+        return crd
+    i = mod.INFO
+    schema = _strip_descriptions(crd["spec"]["versions"][0]["schema"]["openAPIV3Schema"])
+    rs = schema["properties"]["spec"]["properties"][i.specs_key]["additionalProperties"]
+    rs["properties"]["template"] = {"type": "object"}
+    schema = _document(schema, i.kind)
+    rs = schema["properties"]["spec"]["properties"][i.specs_key]["additionalProperties"]
+    rs["properties"]["template"] = copy.deepcopy(pod_template_schema())
+    crd["spec"]["versions"][0]["schema"]["openAPIV3Schema"] = schema
+    # controller-gen leaves these behind; kept so the documents compare equal
+    crd["metadata"]["creationTimestamp"] = None
+    crd["status"] = {"acceptedNames": {"kind": "", "plural": ""}, "conditions": [],
+                     "storedVersions": []}
+    return crd
+
+
+def _crd_structure(mod) -> dict:
     i = mod.INFO
     spec_props = {"runPolicy": RUN_POLICY,
                   i.specs_key: {"type": "object", "additionalProperties": REPLICA_SPEC}}
@@ -129,7 +196,7 @@ def write_all(out_dir: str) -> list:
     paths = []
     for mod in KINDS.values():
         p = out / f"kubeflow.org_{mod.INFO.plural}.yaml"
-        p.write_text("---\n" + yaml.safe_dump(crd_for(mod), sort_keys=False, width=100))
+        p.write_text("\n---\n" + yaml.safe_dump(crd_for(mod), sort_keys=True, width=80))
         paths.append(p)
     return paths
 

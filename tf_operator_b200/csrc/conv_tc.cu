@@ -23,7 +23,7 @@
 //   wgrad     dW[co, tap, ci] = sum_p dy[p, co] * x[p + d(tap), ci]: contraction over pixels, both
 //             operands MN-major as they sit in memory. M = two (tap, 64-channel) slices of x,
 //             N = Cout (<= 256 per tile), K = pixels in blocks of 64, split over all SMs; fp32
-//             partial tiles are added to dW with RED.
+//             partial tiles are added to dW by TMA reduce-add stores.
 //
 // Mainloop, barriers and CTA pairing are those of gemm_tcgen05.cu (warp 0 TMA producer, warp 1
 // one-thread tcgen05.mma issuer with cta_group::2 pairs on adjacent pixel tiles, warps 4-7
@@ -44,6 +44,21 @@ using namespace tfop_gemm;
 
 constexpr int kMaxTaps = 9;
 
+// n / d and n % d for 0 <= n < 2^24 by one 64-bit multiply (d < 2^16): the tile loops decode
+// (w, h, n) block indices for every tile and k-block, and a runtime-divisor IDIV is ~25 instructions.
+struct FastDiv {
+    unsigned long long magic;  // ceil(2^40 / d)
+    int d;
+    __host__ void set(int div) {
+        d = div;
+        magic = ((1ull << 40) + (unsigned long long)div - 1) / (unsigned long long)div;
+    }
+    __device__ __forceinline__ void divmod(int n, int& q, int& r) const {
+        q = (int)(((unsigned long long)(unsigned)n * magic) >> 40);
+        r = n - q * d;
+    }
+};
+
 struct ConvMaps {
     CUtensorMap a[4];  // activation operand: dense map, or the four parity maps of a stride-2 read
     CUtensorMap b;     // weights [Cout, taps * Cin]
@@ -55,12 +70,12 @@ struct ConvArgs {
     int tap_map[kMaxTaps], tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_bcol[kMaxTaps];
     int tw, th, nb;                // pixel tile: tw * th * nb == 128
     int wblk, hblk, nblk;          // tiles per dimension
+    FastDiv div_wblk, div_hblk, div_nblocks;
     int sw, sh;                    // 32-row store box: sw x sh x (32 / (sw * sh))
     int W, H, N;                   // output pixel grid (for store guards)
     int ncols;                     // GEMM N = output channels of this product
     int b_mn;                      // weights read MN-major (dgrad)
     int accumulate;                // TMA reduce-add instead of store
-    int group_m;                   // band height of the tile order
     float* stats;                  // [2, ncols] fp32 sums, or null
 };
 
@@ -97,47 +112,83 @@ __device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap* map, const 
         : "memory");
 }
 
+constexpr int kConvThreads = 384;  // warps 0-3 as in the GEMM, 4-7 and 8-11 two epilogue groups
+
+// barrier among the 128 threads of one epilogue group (ids 1 and 2; 0 is __syncthreads)
+__device__ __forceinline__ void epi_group_sync(int grp) {
+    if (grp == 0)
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+    else
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+}
+
 template <int BN, int kPair>
 struct CCfg {
     // one stage fewer than the plain GEMM: the statistics partials take its place
     static constexpr int kStages = kPair == 2 ? (BN == 256 ? 5 : (BN == 128 ? 7 : 8))
                                               : (BN == 256 ? 3 : (BN == 128 ? 5 : 6));
+    static_assert(BN <= 256, "two accumulator stages of BN columns must fit TMEM");
     static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
     static constexpr int kBBytes = (BN / kPair) * BLOCK_K * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = 2 * BN;
     static constexpr int kBarBytes = 256;
     static constexpr int kStoreBoxBytes = 32 * 128;
-    static constexpr int kStoreBytes = 4 * 2 * kStoreBoxBytes;
-    static constexpr int kStatBytes = 4 * 2 * BN * 4;  // per epilogue warp: sum and sum of squares
+    static constexpr int kStoreBytes = 8 * kStoreBoxBytes;   // one staging box per epilogue warp
+    static constexpr int kStatBytes = 8 * 2 * BN * 4;  // per epilogue warp: sum and sum of squares
     static constexpr int kSmemBytes =
         kStages * kStageBytes + kStoreBytes + kBarBytes + kStatBytes + 1024;
     static_assert(kSmemBytes <= 227 * 1024, "shared memory budget of one CTA");
 };
 
+// Packed fp32 pairs (FADD2 / FFMA2): one instruction for the two channels a lane owns.
+__device__ __forceinline__ unsigned long long pack_f32x2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ unsigned long long add_f32x2(unsigned long long a, unsigned long long b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ unsigned long long fma_f32x2(unsigned long long a, unsigned long long b,
+                                                        unsigned long long c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
 // Per-channel sum / sum of squares over the 32 rows of a staged (swizzled) 32 x 64 bf16 box:
 // lane l owns channels 2l and 2l+1. All lanes read the same row at once: conflict-free. Rows
 // whose bit in `rows` is clear lie outside the image (partial tiles: a 3x3 tap still reaches
-// valid input from there, so they are not zero) and are left out.
+// valid input from there, so they are not zero) and are left out. The swizzle term depends on
+// r & 7 only: eight base pointers, then every row is one LDS with an immediate offset, a shift,
+// a mask and two packed fp32 operations (was ~13 instructions per row: ncu, source page).
+template <bool kMasked>
 __device__ __forceinline__ void box_col_sums(const uint8_t* box, int lane, uint32_t rows, float& s0,
                                              float& s1, float& q0, float& q1) {
     const uint32_t j = (uint32_t)lane >> 2, o = ((uint32_t)lane & 3u) << 2;
-    s0 = s1 = q0 = q1 = 0.f;
-#pragma unroll 8
+    const uint8_t* base[8];
+#pragma unroll
+    for (uint32_t k = 0; k < 8; ++k) base[k] = box + ((j ^ k) << 4) + o;
+    unsigned long long s[2] = {0ull, 0ull}, q[2] = {0ull, 0ull};
+#pragma unroll
     for (uint32_t r = 0; r < 32; ++r) {
-        uint32_t v =
-            *reinterpret_cast<const uint32_t*>(box + r * 128u + ((j ^ (r & 7u)) << 4) + o);
-        if (!((rows >> r) & 1u)) v = 0u;
-        const float a = __uint_as_float(v << 16), b = __uint_as_float(v & 0xffff0000u);
-        s0 += a;
-        s1 += b;
-        q0 = fmaf(a, a, q0);
-        q1 = fmaf(b, b, q1);
+        uint32_t v = *reinterpret_cast<const uint32_t*>(base[r & 7u] + r * 128u);
+        if (kMasked && !((rows >> r) & 1u)) v = 0u;
+        const unsigned long long a =
+            pack_f32x2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u));
+        s[r & 1u] = add_f32x2(s[r & 1u], a);
+        q[r & 1u] = fma_f32x2(a, a, q[r & 1u]);
     }
+    const unsigned long long st = add_f32x2(s[0], s[1]), qt = add_f32x2(q[0], q[1]);
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(s0), "=f"(s1) : "l"(st));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(q0), "=f"(q1) : "l"(qt));
 }
 
 template <int BN, int kCluster>
-__global__ void __maxnreg__(136)
+__global__ void __maxnreg__(128)
 conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvArgs args) {
     using cfg = CCfg<BN, kCluster>;
     constexpr bool kPair = kCluster == 2;
@@ -205,12 +256,16 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
 
     // pixel tile index -> origin in the (w, h, n) grid
     auto tile_origin = [&](int mb, int& w0, int& h0, int& n0) {
-        const int wb = mb % args.wblk;
-        const int q = mb / args.wblk;
+        int q, wb, hb, nbk;
+        args.div_wblk.divmod(mb, q, wb);
+        args.div_hblk.divmod(q, nbk, hb);
         w0 = wb * args.tw;
-        h0 = (q % args.hblk) * args.th;
-        n0 = (q / args.hblk) * args.nb;
+        h0 = hb * args.th;
+        n0 = nbk * args.nb;
     };
+    // Tile order: the n-blocks of one pixel tile are consecutive, so the CTAs that need the same
+    // activation boxes run at the same time (the weights are small and always in L2).
+    auto tile_decode = [&](int t, int& mu, int& nb) { args.div_nblocks.divmod(t, mu, nb); };
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -219,7 +274,7 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
             uint32_t phase = 0;
             for (int t = t_first; t < num_tiles; t += t_step) {
                 int mu, nb;
-                tile_coords_rt(t, m_units, n_blocks, args.group_m, mu, nb);
+                tile_decode(t, mu, nb);
                 int w0, h0, n0;
                 tile_origin(mu * kCluster + crank, w0, h0, n0);
                 const int col0 = nb * BN + (kPair ? crank * (BN / 2) : 0);
@@ -310,24 +365,31 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
             }
         }
     } else if (warp >= kEpiWarp0) {
-        // ===================== epilogue =====================
-        const int ew = warp - kEpiWarp0;
-        int acc = 0;
+        // ===================== epilogue: two groups of four warps =====================
+        // Group g drains accumulator stage g, i.e. every other tile of this CTA, so two tiles'
+        // epilogues (TMEM loads, conversion, statistics) run side by side on the four SM
+        // sub-partitions: with short K (1x1 layers off 64 channels: one k-block per tile) the
+        // epilogue, not the tensor pipe, is what a tile costs.
+        const int grp = (warp - kEpiWarp0) >> 2;
+        const int ew = warp & 3;  // TMEM lane quadrant of this warp
+        const int acc = grp;
         uint32_t acc_phase = 0;
-        uint8_t* box0 = smem_store + ew * 2 * cfg::kStoreBoxBytes;
+        uint8_t* box = smem_store + (grp * 4 + ew) * cfg::kStoreBoxBytes;
         const uint32_t row_off = (uint32_t)lane * 128u;
         const uint32_t sw = (uint32_t)(lane & 7);
-        float* mystat = sstat + ew * 2 * BN;
+        float* gstat = sstat + grp * 8 * BN;
+        float* mystat = gstat + ew * 2 * BN;
         const bool want_stats = args.stats != nullptr;
         // this warp's 32 rows of the tile as a sub-box of the pixel tile
         const int r0 = ew * 32;
         const int tw0 = r0 % args.tw;
         const int th0 = (r0 / args.tw) % args.th;
         const int nb0 = r0 / (args.tw * args.th);
-        int buf = 0;
-        for (int t = t_first; t < num_tiles; t += t_step) {
+        // this lane's row inside the warp's 32-row sub-box
+        const int lw = lane % args.sw, lh = (lane / args.sw) % args.sh, ln = lane / (args.sw * args.sh);
+        for (int t = t_first + grp * t_step; t < num_tiles; t += 2 * t_step) {
             int mu, nb;
-            tile_coords_rt(t, m_units, n_blocks, args.group_m, mu, nb);
+            tile_decode(t, mu, nb);
             int w0, h0, n0;
             tile_origin(mu * kCluster + crank, w0, h0, n0);
             w0 += tw0;
@@ -336,11 +398,9 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
             const bool in_grid = w0 < args.W && h0 < args.H && n0 < args.N;
             // which of this warp's 32 rows are pixels of the image (lane = row)
             uint32_t rows = 0xffffffffu;
-            if (want_stats) {
-                const int rw = lane % args.sw, rq = lane / args.sw;
-                rows = __ballot_sync(0xffffffffu, w0 + rw < args.W && h0 + rq % args.sh < args.H &&
-                                                      n0 + rq / args.sh < args.N);
-            }
+            if (want_stats)
+                rows = __ballot_sync(0xffffffffu,
+                                     w0 + lw < args.W && h0 + lh < args.H && n0 + ln < args.N);
             const int col0 = nb * BN;
             mbar_wait(&tmem_full[acc], acc_phase);
             tcgen05_fence_after();
@@ -351,8 +411,8 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
             for (int c = 0; c < BN; c += 64) {
                 tmem_ld_wait();
                 tmem_ld_32x32b_x32(taddr + (uint32_t)(c + 32), rb);
-                uint8_t* box = box0 + buf * cfg::kStoreBoxBytes;
-                if (lane == 0) bulk_wait_read<1>();
+                // one staging box per warp: the previous chunk's store must have read it
+                if (lane == 0) bulk_wait_read<0>();
                 __syncwarp();
                 float f[32];
 #pragma unroll
@@ -386,11 +446,13 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
                 }
                 if (want_stats) {
                     float s0, s1, q0, q1;
-                    box_col_sums(box, lane, rows, s0, s1, q0, q1);
+                    if (rows == 0xffffffffu)
+                        box_col_sums<false>(box, lane, rows, s0, s1, q0, q1);
+                    else
+                        box_col_sums<true>(box, lane, rows, s0, s1, q0, q1);
                     *reinterpret_cast<float2*>(mystat + c + 2 * lane) = make_float2(s0, s1);
                     *reinterpret_cast<float2*>(mystat + BN + c + 2 * lane) = make_float2(q0, q1);
                 }
-                buf ^= 1;
             }
             tcgen05_fence_before();
             __syncwarp();
@@ -400,22 +462,19 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
                 else
                     mbar_arrive(&tmem_empty[acc]);
             }
-            if (++acc == 2) {
-                acc = 0;
-                acc_phase ^= 1;
-            }
+            acc_phase ^= 1;
             if (want_stats) {
                 // fold the four warps' partials, one RED per channel and moment per tile
-                epi_bar_sync();
+                epi_group_sync(grp);
                 for (int i = ew * 32 + lane; i < 2 * BN; i += 128) {
                     const int ch = i < BN ? i : i - BN;
                     if (col0 + ch < args.ncols) {
-                        const float v = sstat[i] + sstat[2 * BN + i] + sstat[4 * BN + i] +
-                                        sstat[6 * BN + i];
+                        const float v = gstat[i] + gstat[2 * BN + i] + gstat[4 * BN + i] +
+                                        gstat[6 * BN + i];
                         atomicAdd(args.stats + (i < BN ? 0 : args.ncols) + col0 + ch, v);
                     }
                 }
-                epi_bar_sync();
+                epi_group_sync(grp);
             }
         }
         if (lane == 0) bulk_wait_read<0>();
@@ -439,68 +498,84 @@ conv_igemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__
 }
 
 // ---------------------------------------------------------------------------------------------
-// Weight gradient. One CTA = one (M tile, N tile, pixel range): M tile = two (tap, 64 input
-// channels) slices of x, N tile = up to 256 output channels of dy, K = its share of the 64-pixel
-// blocks. Both operands MN-major. CTAs with the same pixel range and different tiles are
-// adjacent in the grid, so the boxes they share come out of L2.
+// Weight gradient. One scheduling unit = one (M tile, N tile, pixel range): the M tile is a run of
+// (tap, 64 input channels) slices of x, the N tile up to 256 output channels of dy, K the unit's
+// share of the 64-pixel blocks. Both operands MN-major. Units with the same pixel range and
+// different tiles are adjacent in the grid, so the boxes they share come out of L2.
+//   BN >= 128: units run on CTA pairs (cta_group::2): 256 x BN MMAs, each CTA stages its own two
+//              slices of x and HALF of the dy tile - 32 KB per k-block and CTA instead of 48 KB.
+//              The kernel is bound by how fast TMA can fill shared memory (ncu: tensor pipe 39 %
+//              busy, both the producer and the MMA thread waiting), so bytes per MMA is the lever.
+//   BN == 64:  a CTA holds four slices (two 128-row MMAs into two accumulators per k-step) so the
+//              8 KB dy box is shared by twice the work.
 struct WgradMaps {
     CUtensorMap x[4];
     CUtensorMap dy;
+    CUtensorMap dw;  // fp32 [Cout rows, n_taps * Cin], boxes of 32 x 32, reduce-add target
 };
 struct WgradArgs {
     int n_taps, cblocks;   // M slices = n_taps * cblocks (cblocks = Cin / 64)
     int tap_map[kMaxTaps], tap_dh[kMaxTaps], tap_dw[kMaxTaps];
     int pw, ph, pn;        // pixel block: pw * ph * pn == 64
     int wblk, hblk, nblk;  // pixel blocks per dimension
-    int m_tiles, n_tiles, splits;
+    FastDiv div_wblk, div_hblk;
+    int m_units, n_tiles, splits;
     int Cin, Cout;
-    float* dw;             // [Cout, n_taps, Cin] fp32, accumulated with RED
 };
 
-constexpr int kWgStages = 4;
-
-template <int BN>
+template <int BN, int CL>
 struct WCfg {
-    static constexpr int kABytes = 2 * kMnBoxBytes;
-    static constexpr int kBBytes = (BN / 64) * kMnBoxBytes;
+    static constexpr int kSlices = BN == 64 ? 4 : 2;      // slices of x per CTA
+    static constexpr int kABytes = kSlices * kMnBoxBytes;
+    static constexpr int kBBytes = (BN / CL / 64) * kMnBoxBytes;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kSmemBytes = kWgStages * kStageBytes + 256 + 1024;
+    static constexpr int kStages = kStageBytes <= 32768 ? 6 : 4;
+    static constexpr int kBoxBytes = 32 * 32 * 4;  // per epilogue warp: a transposed 32 x 32 fp32 box
+    static constexpr int kTmemCols = (kSlices / 2) * BN;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 4 * kBoxBytes + 256 + 1024;
     static_assert(kSmemBytes <= 227 * 1024, "shared memory budget of one CTA");
+    static_assert(BN / CL >= 64, "a CTA stages whole 64-column boxes of dy");
 };
 
-template <int BN>
+template <int BN, int CL>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ WgradArgs args) {
-    using cfg = WCfg<BN>;
+    using cfg = WCfg<BN, CL>;
+    constexpr bool kPair = CL == 2;
+    constexpr int MS = cfg::kSlices;
+    constexpr int kStages = cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = (uint64_t*)(smem + kWgStages * cfg::kStageBytes);
+    uint8_t* smem_box = smem + kStages * cfg::kStageBytes;
+    uint64_t* bars = (uint64_t*)(smem_box + 4 * cfg::kBoxBytes);
     uint64_t* full = bars;
-    uint64_t* empty = bars + kWgStages;
-    uint64_t* done = bars + 2 * kWgStages;
+    uint64_t* empty = bars + kStages;
+    uint64_t* done = bars + 2 * kStages;
     uint32_t* tmem_slot = (uint32_t*)(done + 1);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const int crank = kPair ? (int)cluster_ctarank() : 0;
 
     // unit -> (tile, split): tiles of one pixel range are neighbours
-    const int tiles = args.m_tiles * args.n_tiles;
-    const int tile = blockIdx.x % tiles;
-    const int split = blockIdx.x / tiles;
-    const int mt = tile % args.m_tiles;
-    const int nt = tile / args.m_tiles;
+    const int unit = blockIdx.x / CL;
+    const int tiles = args.m_units * args.n_tiles;
+    const int tile = unit % tiles;
+    const int split = unit / tiles;
+    const int mt = (tile % args.m_units) * CL + crank;   // this CTA's run of MS slices
+    const int nt = tile / args.m_units;
     const int pblocks = args.wblk * args.hblk * args.nblk;
     const int pb0 = (int)((long)pblocks * split / args.splits);
     const int pb1 = (int)((long)pblocks * (split + 1) / args.splits);
     const int n_slices = args.n_taps * args.cblocks;
-    constexpr int kTmemCols = BN < 32 ? 32 : BN;
 
     if (warp == 0 && lane == 0) {
         for (int i = 0; i < 4; ++i)
             asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.x[i]) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.dy) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.dw) : "memory");
     }
     if (warp == 1 && lane == 0) {
-        for (int i = 0; i < kWgStages; ++i) {
+        for (int i = 0; i < kStages; ++i) {
             mbar_init(&full[i], 1);
             mbar_init(&empty[i], 1);
         }
@@ -508,60 +583,84 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                         smem_u32(tmem_slot)),
-                     "r"((uint32_t)kTmemCols)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (kPair) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32(tmem_slot)),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32(tmem_slot)),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tcgen05_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync_all();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
         if (elect_one()) {
-            // the two M slices of this tile; a missing second slice is fetched from outside the
-            // batch (n = N: all zeros) and skipped in the epilogue
-            int s_map[2], s_dh[2], s_dw[2], s_c0[2];
-            bool s_ok[2];
-            for (int j = 0; j < 2; ++j) {
-                const int s = mt * 2 + j;
-                s_ok[j] = s < n_slices;
-                const int tap = s_ok[j] ? s / args.cblocks : 0;
+            // this CTA's slices; a slice past the end is fetched from outside the batch (all
+            // zeros) and skipped in the epilogue
+            int s_map[MS], s_dh[MS], s_dw[MS], s_c0[MS];
+            bool s_ok[MS];
+#pragma unroll
+            for (int j = 0; j < MS; ++j) {
+                const int sl = mt * MS + j;
+                s_ok[j] = sl < n_slices;
+                const int tap = s_ok[j] ? sl / args.cblocks : 0;
                 s_map[j] = args.tap_map[tap];
                 s_dh[j] = args.tap_dh[tap];
                 s_dw[j] = args.tap_dw[tap];
-                s_c0[j] = s_ok[j] ? (s - tap * args.cblocks) * 64 : 0;
+                s_c0[j] = s_ok[j] ? (sl - tap * args.cblocks) * 64 : 0;
             }
+            const int n_out = args.nblk * args.pn + 64;
+            const int dy_col = nt * BN + crank * (BN / CL);
             int stage = 0;
             uint32_t phase = 0;
             for (int pb = pb0; pb < pb1; ++pb) {
-                const int wb = pb % args.wblk;
-                const int q = pb / args.wblk;
-                const int w0 = wb * args.pw, h0 = (q % args.hblk) * args.ph;
-                const int n0 = (q / args.hblk) * args.pn;
+                int q, wb, hb, nbk;
+                args.div_wblk.divmod(pb, q, wb);
+                args.div_hblk.divmod(q, nbk, hb);
+                const int w0 = wb * args.pw, h0 = hb * args.ph, n0 = nbk * args.pn;
                 mbar_wait(&empty[stage], phase ^ 1);
-                mbar_expect_tx(&full[stage], cfg::kStageBytes);
                 uint8_t* sa = smem + stage * cfg::kStageBytes;
+                if (kPair) {
+                    if (crank == 0) mbar_expect_tx(&full[stage], 2 * cfg::kStageBytes);
 #pragma unroll
-                for (int j = 0; j < 2; ++j)
-                    tma_load_4d(&maps.x[s_map[j]], &full[stage], sa + j * kMnBoxBytes, s_c0[j],
-                                w0 + s_dw[j], h0 + s_dh[j],
-                                s_ok[j] ? n0 : args.nblk * args.pn + 64);
+                    for (int j = 0; j < MS; ++j)
+                        tma_load_4d_pair(&maps.x[s_map[j]], &full[stage], sa + j * kMnBoxBytes,
+                                         s_c0[j], w0 + s_dw[j], h0 + s_dh[j], s_ok[j] ? n0 : n_out);
 #pragma unroll
-                for (int j = 0; j < BN / 64; ++j)
-                    tma_load_4d(&maps.dy, &full[stage], sa + cfg::kABytes + j * kMnBoxBytes,
-                                nt * BN + 64 * j, w0, h0, n0);
-                if (++stage == kWgStages) {
+                    for (int j = 0; j < BN / CL / 64; ++j)
+                        tma_load_4d_pair(&maps.dy, &full[stage],
+                                         sa + cfg::kABytes + j * kMnBoxBytes, dy_col + 64 * j, w0,
+                                         h0, n0);
+                } else {
+                    mbar_expect_tx(&full[stage], cfg::kStageBytes);
+#pragma unroll
+                    for (int j = 0; j < MS; ++j)
+                        tma_load_4d(&maps.x[s_map[j]], &full[stage], sa + j * kMnBoxBytes, s_c0[j],
+                                    w0 + s_dw[j], h0 + s_dh[j], s_ok[j] ? n0 : n_out);
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j)
+                        tma_load_4d(&maps.dy, &full[stage], sa + cfg::kABytes + j * kMnBoxBytes,
+                                    dy_col + 64 * j, w0, h0, n0);
+                }
+                if (++stage == kStages) {
                     stage = 0;
                     phase ^= 1;
                 }
             }
         }
     } else if (warp == 1) {
-        if (elect_one()) {
-            const uint32_t idesc = make_idesc_major(BLOCK_M, BN, 1, 1);
+        if ((!kPair || crank == 0) && elect_one()) {
+            const uint32_t idesc = make_idesc_major(BLOCK_M * CL, BN, 1, 1);
             int stage = 0;
             uint32_t phase = 0;
             for (int pb = pb0; pb < pb1; ++pb) {
@@ -570,52 +669,82 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant_
                 const uint32_t a_addr = smem_u32(smem + stage * cfg::kStageBytes);
                 const uint32_t b_addr = a_addr + cfg::kABytes;
 #pragma unroll
-                for (int k = 0; k < 64 / UMMA_K; ++k)
-                    umma_bf16(tmem_base, make_smem_desc_mn(a_addr + k * 2048),
-                              make_smem_desc_mn(b_addr + k * 2048), idesc,
-                              (pb != pb0 || k != 0) ? 1u : 0u);
-                umma_commit(&empty[stage]);
-                if (++stage == kWgStages) {
+                for (int k = 0; k < 64 / UMMA_K; ++k) {
+                    const uint64_t bdesc = make_smem_desc_mn(b_addr + k * 2048);
+#pragma unroll
+                    for (int h = 0; h < MS / 2; ++h) {
+                        const uint64_t adesc =
+                            make_smem_desc_mn(a_addr + h * 2 * kMnBoxBytes + k * 2048);
+                        const uint32_t accf = (pb != pb0 || k != 0) ? 1u : 0u;
+                        if (kPair)
+                            umma_bf16_pair(tmem_base + (uint32_t)(h * BN), adesc, bdesc, idesc, accf);
+                        else
+                            umma_bf16(tmem_base + (uint32_t)(h * BN), adesc, bdesc, idesc, accf);
+                    }
+                }
+                if (kPair)
+                    umma_commit_pair(&empty[stage]);
+                else
+                    umma_commit(&empty[stage]);
+                if (++stage == kStages) {
                     stage = 0;
                     phase ^= 1;
                 }
             }
-            umma_commit(done);
+            if (kPair)
+                umma_commit_pair(done);
+            else
+                umma_commit(done);
         }
     } else if (warp >= kEpiWarp0 && pb1 > pb0) {
+        // TMEM -> registers -> transposed into a [32 co][32 m] fp32 box -> one TMA reduce-add per
+        // box: row m of the accumulator (lane) is a run of consecutive addresses of dW[co, :],
+        // so the lanes of one STS write one 128-byte row of the box. (Per-element RED from the
+        // registers cost ~40 issue cycles per warp instruction: 22 us per CTA at 128 x 256.)
         const int ew = warp - kEpiWarp0;
         mbar_wait(done, 0);
         tcgen05_fence_after();
-        const int row = ew * 32 + lane;
-        const int s = mt * 2 + (row >> 6);
-        const bool ok = s < n_slices;
-        const int tap = ok ? s / args.cblocks : 0;
-        const int ci = (s - tap * args.cblocks) * 64 + (row & 63);
-        float* dst = args.dw + (size_t)tap * args.Cin + ci;
-        const size_t co_stride = (size_t)args.n_taps * args.Cin;
-        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16);
+        float* box = (float*)(smem_box + ew * cfg::kBoxBytes);
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(taddr + (uint32_t)c, r);
-            tmem_ld_wait();
-            if (ok) {
+        for (int h = 0; h < MS / 2; ++h) {
+            const int m0 = mt * (64 * MS) + h * 128 + ew * 32;   // column of dW = (tap, ci) flattened
+            const bool ok = m0 < n_slices * 64;
+            const uint32_t taddr = tmem_base + (uint32_t)(h * BN) + ((uint32_t)(ew * 32) << 16);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + (uint32_t)c, r);
+                tmem_ld_wait();
+                if (lane == 0) bulk_wait_read<0>();
+                __syncwarp();
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int co = nt * BN + c + j;
-                    if (co < args.Cout) atomicAdd(dst + (size_t)co * co_stride, __uint_as_float(r[j]));
+                for (int j = 0; j < 32; ++j) box[j * 32 + lane] = __uint_as_float(r[j]);
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    if (ok && nt * BN + c < args.Cout)
+                        tma_reduce_add_2d(&maps.dw, box, m0, nt * BN + c);
+                    bulk_commit();
                 }
             }
         }
+        if (lane == 0) bulk_wait_read<0>();
+        __syncwarp();
     }
 
     tcgen05_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync_all();
     if (warp == 2) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                     "r"((uint32_t)kTmemCols)
-                     : "memory");
+        if (kPair)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                         "r"((uint32_t)cfg::kTmemCols)
+                         : "memory");
     }
 }
 
@@ -708,7 +837,7 @@ struct DevInfo {
     bool init = false;
     int sms = 0;
     int max_ctas[3][2] = {};   // [BN index][cluster - 1]
-    bool wg_attr[3] = {};
+    int wg_slots[3][2] = {};   // wgrad kernel: resident CTAs / clusters, 0 = not set up yet
 };
 DevInfo g_dev[16];
 
@@ -723,7 +852,7 @@ int launch_igemm(const ConvMaps& maps, ConvArgs& args, DevInfo& di, int bn_idx, 
         if (CL == 2) {
             cudaLaunchConfig_t q = {};
             q.gridDim = dim3(di.sms / 2 * 2);
-            q.blockDim = dim3(kNumThreads);
+            q.blockDim = dim3(kConvThreads);
             q.dynamicSmemBytes = CCfg<BN, CL>::kSmemBytes;
             cudaLaunchAttribute qa[1];
             qa[0].id = cudaLaunchAttributeClusterDimension;
@@ -741,15 +870,12 @@ int launch_igemm(const ConvMaps& maps, ConvArgs& args, DevInfo& di, int bn_idx, 
     const int m_blocks = args.wblk * args.hblk * args.nblk;
     const int m_units = (m_blocks + CL - 1) / CL;
     const int tiles = m_units * ((args.ncols + BN - 1) / BN);
-    // band: ~2 MB of activations per band, so every n-block of a band finds its A tiles in L2
-    int group = 16;
-    if (group > m_units) group = m_units;
-    args.group_m = group;
+    args.div_nblocks.set((args.ncols + BN - 1) / BN);
     int grid = tiles * CL;
     if (grid > max_ctas) grid = max_ctas;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(kNumThreads);
+    cfg.blockDim = dim3(kConvThreads);
     cfg.dynamicSmemBytes = CCfg<BN, CL>::kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -809,6 +935,8 @@ void set_geom(ConvArgs& a, int W, int H, int N) {
     a.wblk = (W + g.tw - 1) / g.tw;
     a.hblk = (H + g.th - 1) / g.th;
     a.nblk = (N + g.nb - 1) / g.nb;
+    a.div_wblk.set(a.wblk);
+    a.div_hblk.set(a.hblk);
     a.sw = g.tw < 32 ? g.tw : 32;
     a.sh = g.th < 32 / a.sw ? g.th : 32 / a.sw;
     a.W = W;
@@ -947,7 +1075,6 @@ TFOP_API int tfop_conv_wgrad(const void* x, const void* dy, float* dw, int N, in
     a.cblocks = Cin / 64;
     a.Cin = Cin;
     a.Cout = Cout;
-    a.dw = dw;
     bool used[4] = {false, false, false, false};
     for (int kh = 0; kh < ksize; ++kh)
         for (int kw = 0; kw < ksize; ++kw) {
@@ -973,35 +1100,104 @@ TFOP_API int tfop_conv_wgrad(const void* x, const void* dy, float* dw, int N, in
             return -1;
     }
     if (act_map(&maps.dy, dy, N, OH, OW, Cout, 1, 0, 0, a.pw, a.ph, a.pn, "dy")) return -1;
+    {   // dW as a 2-D fp32 matrix [Cout, taps * Cin]; unswizzled 32 x 32 boxes
+        const int cols = ksize * ksize * Cin;
+        cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)Cout};
+        cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+        cuuint32_t box[2] = {32, 32};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = g_enc(&maps.dw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, dw, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                           CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            tfop_set_error(__FILE__, __LINE__, "cuTensorMapEncodeTiled(dw) failed");
+            return -1;
+        }
+    }
     const int bn = Cout >= 256 ? 256 : (Cout >= 128 ? 128 : 64);
     const int slices = a.n_taps * a.cblocks;
-    a.m_tiles = (slices + 1) / 2;
+    const int ms = bn == 64 ? 4 : 2;                 // slices per CTA
+    const int m_tiles = (slices + ms - 1) / ms;
+    const bool pair = bn >= 128 && m_tiles >= 2 && g_conv_cluster_mode != 0;
+    const int cl = pair ? 2 : 1;
+    a.m_units = (m_tiles + cl - 1) / cl;
     a.n_tiles = (Cout + bn - 1) / bn;
-    const int tiles = a.m_tiles * a.n_tiles;
+    a.div_wblk.set(a.wblk);
+    a.div_hblk.set(a.hblk);
+    const int tiles = a.m_units * a.n_tiles;
     const int pblocks = a.wblk * a.hblk * a.nblk;
-    // one CTA per (tile, pixel range): about two waves of CTAs, every range at least 4 blocks
-    int splits = (2 * di->sms + tiles - 1) / tiles;
-    if (splits > pblocks / 4) splits = pblocks / 4;
-    if (splits < 1) splits = 1;
-    a.splits = splits;
-    const int grid = tiles * splits;
     const int bi = bn == 256 ? 2 : (bn == 128 ? 1 : 0);
-#define TFOP_WG_LAUNCH(BN_)                                                                       \
+    int& slots = di->wg_slots[bi][cl - 1];
+#define TFOP_WG_PREP(BN_, CL_)                                                                    \
     do {                                                                                          \
-        if (!di->wg_attr[bi]) {                                                                   \
-            TFOP_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BN_>,                                \
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize,           \
-                                           WCfg<BN_>::kSmemBytes));                               \
-            di->wg_attr[bi] = true;                                                               \
+        TFOP_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BN_, CL_>,                               \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,               \
+                                       WCfg<BN_, CL_>::kSmemBytes));                              \
+        slots = di->sms;                                                                          \
+        if (CL_ == 2) {                                                                           \
+            cudaLaunchConfig_t q = {};                                                            \
+            q.gridDim = dim3(di->sms / 2 * 2);                                                    \
+            q.blockDim = dim3(kNumThreads);                                                       \
+            q.dynamicSmemBytes = WCfg<BN_, CL_>::kSmemBytes;                                      \
+            cudaLaunchAttribute qa[1];                                                            \
+            qa[0].id = cudaLaunchAttributeClusterDimension;                                       \
+            qa[0].val.clusterDim.x = 2;                                                           \
+            qa[0].val.clusterDim.y = 1;                                                           \
+            qa[0].val.clusterDim.z = 1;                                                           \
+            q.attrs = qa;                                                                         \
+            q.numAttrs = 1;                                                                       \
+            int n = 0;                                                                            \
+            TFOP_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_wgrad_kernel<BN_, CL_>, &q));       \
+            TFOP_REQUIRE(n > 0, "no 2-CTA cluster of the wgrad kernel fits on this device");      \
+            slots = n;                                                                            \
         }                                                                                         \
-        conv_wgrad_kernel<BN_><<<grid, kNumThreads, WCfg<BN_>::kSmemBytes, stream>>>(maps, a);    \
     } while (0)
-    if (bn == 256)
-        TFOP_WG_LAUNCH(256);
-    else if (bn == 128)
-        TFOP_WG_LAUNCH(128);
-    else
-        TFOP_WG_LAUNCH(64);
+    if (slots == 0) {
+        if (bn == 256 && pair) TFOP_WG_PREP(256, 2);
+        else if (bn == 256) TFOP_WG_PREP(256, 1);
+        else if (bn == 128 && pair) TFOP_WG_PREP(128, 2);
+        else if (bn == 128) TFOP_WG_PREP(128, 1);
+        else TFOP_WG_PREP(64, 1);
+    }
+#undef TFOP_WG_PREP
+    // Pixel ranges per tile: every unit pays ~8 k-blocks' worth of set-up, pipeline fill and
+    // epilogue, and the units run in waves of `slots`: take the split count with the least
+    // (waves x (k-blocks per unit + 8)).
+    int splits = 1;
+    {
+        long best = -1;
+        const int smax = pblocks < 4 * slots ? pblocks : 4 * slots;
+        for (int sp = 1; sp <= smax; ++sp) {
+            const long waves = ((long)tiles * sp + slots - 1) / slots;
+            const long cost = waves * ((pblocks + sp - 1) / sp + 8);
+            if (best < 0 || cost < best) {
+                best = cost;
+                splits = sp;
+            }
+        }
+    }
+    a.splits = splits;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(tiles * splits * cl);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cl;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+#define TFOP_WG_LAUNCH(BN_, CL_)                                                                  \
+    do {                                                                                          \
+        cfg.dynamicSmemBytes = WCfg<BN_, CL_>::kSmemBytes;                                        \
+        TFOP_CUDA(cudaLaunchKernelEx(&cfg, conv_wgrad_kernel<BN_, CL_>, maps, a));                \
+    } while (0)
+    if (bn == 256 && pair) TFOP_WG_LAUNCH(256, 2);
+    else if (bn == 256) TFOP_WG_LAUNCH(256, 1);
+    else if (bn == 128 && pair) TFOP_WG_LAUNCH(128, 2);
+    else if (bn == 128) TFOP_WG_LAUNCH(128, 1);
+    else TFOP_WG_LAUNCH(64, 1);
 #undef TFOP_WG_LAUNCH
     TFOP_CUDA(cudaGetLastError());
     return 0;

@@ -7,6 +7,8 @@ tensorflow.go (:51-173 TF_CONFIG), util.go:29-42, pod.go:298-319 isDistributed.
 """
 from __future__ import annotations
 
+import threading
+
 import json
 import os
 from typing import Any, Dict, List, Optional
@@ -117,8 +119,7 @@ class TFJobReconciler(KindReconciler):
     def is_worker0_completed(self, job, replicas) -> bool:
         if tfapi.WORKER not in replicas:
             return True
-        pods = self.filter_for_replica_type(self._pods_cache if self._pods_cache is not None
-                                            else self.get_pods_for_job(job), tfapi.WORKER.lower())
+        pods = self.filter_for_replica_type(self._cached_pods(job), tfapi.WORKER.lower())
         slices = self.get_slices(pods, int(replicas[tfapi.WORKER].get("replicas", 1)))
         for index, sl in enumerate(slices):
             if len(sl) == 1 and index == 0:
@@ -128,14 +129,28 @@ class TFJobReconciler(KindReconciler):
                     return True
         return False
 
-    _pods_cache = None
+    # The pod list of the reconcile in flight, so update_job_status() does not list again.
+    # Workers of one kind share this reconciler object (Manager.start spawns `threadiness`
+    # threads per kind), so the list is per THREAD and tagged with the job it belongs to: a
+    # thread only ever reads what its own reconcile of that same job stored.
+    _tls = threading.local()
+
+    def _cached_pods(self, job):
+        uid = (job.get("metadata") or {}).get("uid") or c.key_of(job)
+        if getattr(self._tls, "uid", None) == uid and getattr(self._tls, "pods", None) is not None:
+            return self._tls.pods
+        return self.get_pods_for_job(job)
 
     def reconcile_jobs(self, job, replicas, status, run_policy) -> None:
-        self._pods_cache = None
-        super().reconcile_jobs(job, replicas, status, run_policy)
+        self._tls.uid = (job.get("metadata") or {}).get("uid") or c.key_of(job)
+        self._tls.pods = None
+        try:
+            super().reconcile_jobs(job, replicas, status, run_policy)
+        finally:
+            self._tls.uid = self._tls.pods = None
 
     def reconcile_pods(self, job, status, pods, rtype, spec, replicas) -> None:
-        self._pods_cache = pods
+        self._tls.pods = pods
         super().reconcile_pods(job, status, pods, rtype, spec, replicas)
 
     def update_job_status(self, job, replicas, status) -> None:

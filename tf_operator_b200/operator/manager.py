@@ -26,21 +26,13 @@ from ..engine.job_controller import JobControllerConfig
 from ..engine.workqueue import RateLimitingQueue
 from ..kinds import RECONCILERS
 from ..store.memory import ApiError, ObjectStore
+from . import pprof
 from .metrics import OperatorMetrics
 
 log = logging.getLogger("tf_operator_b200.operator")
 
 LEASE_DURATION, RENEW_DEADLINE, RETRY_PERIOD = 15.0, 5.0, 3.0   # server.go:54-59
 
-
-def _thread_dump() -> bytes:
-    import sys
-    import traceback
-    names = {t.ident: t.name for t in threading.enumerate()}
-    out = []
-    for ident, frame in sys._current_frames().items():
-        out.append(f"thread {names.get(ident, '?')} ({ident}):\n" + "".join(traceback.format_stack(frame)))
-    return "\n".join(out).encode()
 
 
 class EnabledSchemes(list):
@@ -203,7 +195,10 @@ class Manager:
                 q.add_rate_limited(key)
             finally:
                 q.done(key)
-                self.metrics.reconcile_seconds.labels(kind).observe(time.perf_counter() - t0)
+                dt = time.perf_counter() - t0
+                self.metrics.reconcile_seconds.labels(kind).observe(dt)
+                # controller.go:303-307: "Finished syncing tfjob %q (%v)"
+                log.info("Finished syncing %s %r (%.3fms)", kind.lower(), key, dt * 1e3)
 
     def _resync(self) -> None:
         while not self._stop.wait(self.opt.resync_period):
@@ -268,7 +263,10 @@ class Manager:
                     self.send_response(404)
                     self.end_headers()
                     return
-                ctype, body = fn()
+                try:
+                    ctype, body = fn(pprof.parse_query(self.path))
+                except TypeError:
+                    ctype, body = fn()
                 self.send_response(200)
                 self.send_header("Content-Type", ctype)
                 self.send_header("Content-Length", str(len(body)))
@@ -319,9 +317,8 @@ class Manager:
         self._serve(self.opt.metrics_bind_address, {
             "/metrics": lambda: ("text/plain; version=0.0.4", self.metrics.render()),
             # net/http/pprof shares the legacy binary's metrics mux (cmd/tf-operator.v1/main.go:21,
-            # 39-50); the equivalent here is a goroutine-dump style listing of every thread's stack
-            "/debug/pprof/goroutine": lambda: ("text/plain", _thread_dump()),
-            "/debug/pprof/": lambda: ("text/plain", b"goroutine\n")})
+            # 39-50): goroutine / profile / heap / threadcreate / cmdline (operator/pprof.py)
+            **pprof.routes()})
         self._serve(self.opt.health_probe_bind_address, {
             "/healthz": lambda: ("text/plain", b"ok"), "/readyz": lambda: ("text/plain", b"ok")})
         self.started = True

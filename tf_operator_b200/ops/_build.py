@@ -48,11 +48,11 @@ def _digest(path: Path) -> str:
     return h.hexdigest()
 
 
-def _compile_one(nvcc: str, src: Path, verbose: bool) -> Path:
+def _compile_one(nvcc: str, src: Path, verbose: bool, force: bool = False) -> Path:
     obj = OBJDIR / (src.stem + ".o")
     stamp = OBJDIR / (src.stem + ".sha")
     dig = _digest(src)
-    if obj.exists() and stamp.exists() and stamp.read_text() == dig:
+    if not force and obj.exists() and stamp.exists() and stamp.read_text() == dig:
         return obj
     cmd = [nvcc, *NVCC_FLAGS, "-I", str(CSRC), "-c", str(src), "-o", str(obj)]
     if verbose:
@@ -67,8 +67,11 @@ def _compile_one(nvcc: str, src: Path, verbose: bool) -> Path:
     return obj
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every csrc/*.cu for sm_100a and link the shared library."""
+def build(force: bool = False, verbose: bool = False, recompile=()) -> Path:
+    """Compile every csrc/*.cu for sm_100a and link the shared library. Sources whose stamp
+    (content + headers + flags) is unchanged keep their object file; ``recompile`` names source
+    stems that are compiled regardless - the driver's build check passes the hot kernels there
+    so that nvcc demonstrably runs on this box even when every stamp matches."""
     nvcc = _nvcc()
     OBJDIR.mkdir(parents=True, exist_ok=True)
     if force:
@@ -76,9 +79,9 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             f.unlink()
     srcs = _sources()
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
-        objs = list(ex.map(lambda s: _compile_one(nvcc, s, verbose), srcs))
+        objs = list(ex.map(lambda s: _compile_one(nvcc, s, verbose, s.stem in recompile), srcs))
     newest = max(o.stat().st_mtime for o in objs)
-    if force or not LIB.exists() or LIB.stat().st_mtime < newest:
+    if force or recompile or not LIB.exists() or LIB.stat().st_mtime < newest:
         cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
                "-Xcompiler", "-fPIC", "-o", str(LIB), *map(str, objs)]
         res = subprocess.run(cmd, capture_output=True, text=True)
