@@ -1,0 +1,180 @@
+"""Data-plane life cycle at the launcher's rendezvous store (launcher/rendezvous.py): job-uid
+scoped keys, gang generations across replica restarts, descriptor passing, clean-up on job
+deletion. Behavioural reference: a retryable replica is re-created under the same name
+(pkg/controller.v1/tensorflow/pod.go:140-159) and the e2e suite re-creates a whole job under the
+same name (py/kubeflow/tf_operator/simple_tfjob_tests.py:26-90, --num_trials 2)."""
+import os
+import threading
+import time
+
+import pytest
+
+from tf_operator_b200.launcher.rendezvous import RendezvousClient, RendezvousServer
+
+
+@pytest.fixture()
+def srv():
+    s = RendezvousServer().start()
+    yield s
+    s.stop()
+
+
+def _run(fns):
+    out, errs = [None] * len(fns), []
+
+    def call(i, fn):
+        try:
+            out[i] = fn()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+    ts = [threading.Thread(target=call, args=(i, f)) for i, f in enumerate(fns)]
+    [t.start() for t in ts]
+    [t.join(20) for t in ts]
+    assert not errs, errs
+    return out
+
+
+def test_first_gang_forms_generation_zero_and_exchanges_handles(srv):
+    scope = "ns/job/uid-1/comm0"
+
+    def rank(r):
+        c = RendezvousClient(srv.addr)
+        g = c.join(scope, r, 3)
+        vals = c.all_gather(f"{scope}/g{g}/ipc", r, 3, f"handle-{r}".encode())
+        c.barrier(f"{scope}/g{g}/ready", 3)
+        c.close()
+        return g, vals
+    res = _run([lambda r=r: rank(r) for r in range(3)])
+    assert all(g == 0 for g, _ in res)
+    assert all(v == [b"handle-0", b"handle-1", b"handle-2"] for _, v in res)
+
+
+def test_restarted_rank_opens_a_new_generation_and_stale_keys_are_gone(srv):
+    scope = "ns/job/uid-1/comm0"
+    _run([lambda r=r: RendezvousClient(srv.addr).join(scope, r, 2) for r in range(2)])
+    c = RendezvousClient(srv.addr)
+    c.set(f"{scope}/g0/ipc/0", b"old-0")
+    c.set(f"{scope}/g0/ipc/1", b"old-1")
+    c.add(f"{scope}/g0/ready/count", 2)
+    # rank 1 is re-created by the operator: it must NOT see rank 0's old handle (freed memory)
+    joined = {}
+
+    def rejoin_1():
+        cli = RendezvousClient(srv.addr)
+        g = cli.join(scope, 1, 2, timeout=10)
+        joined[1] = g
+        return cli.all_gather(f"{scope}/g{g}/ipc", 1, 2, b"new-1")
+    t = threading.Thread(target=rejoin_1)
+    t.start()
+    time.sleep(0.3)
+    assert 1 not in joined                      # waits for the rest of the gang in generation 1
+    assert srv.keys(f"{scope}/g0/") == []       # generation 0 dropped the moment it was superseded
+    with pytest.raises(TimeoutError):
+        c.get(f"{scope}/g0/ipc/0", timeout=0.2)
+    # rank 0 times out in its collective, exits 138, is re-created and joins too
+    cli0 = RendezvousClient(srv.addr)
+    g0 = cli0.join(scope, 0, 2, timeout=10)
+    vals0 = cli0.all_gather(f"{scope}/g{g0}/ipc", 0, 2, b"new-0")
+    t.join(10)
+    assert g0 == joined[1] == 1 and vals0 == [b"new-0", b"new-1"]
+
+
+def test_waiter_of_a_superseded_generation_rejoins_by_itself(srv):
+    scope = "ns/job/uid-2/comm0"
+    _run([lambda r=r: RendezvousClient(srv.addr).join(scope, r, 3) for r in range(3)])
+    from tf_operator_b200.launcher.rendezvous import Replaced
+    got, zombie = {}, []
+
+    def join(r, delay, who):
+        time.sleep(delay)
+        try:
+            got[who] = RendezvousClient(srv.addr).join(scope, r, 3, timeout=15)
+        except Replaced as e:
+            zombie.append((who, e))
+    # rank 0 restarts first (-> generation 1) and waits. Then rank 2 restarts twice in a row: its
+    # second incarnation opens generation 2. Rank 0's pending join is superseded and re-joins by
+    # itself; rank 2's first incarnation learns it has been replaced and gives up; rank 1 follows.
+    ts = [threading.Thread(target=join, args=(0, 0.0, "r0")),
+          threading.Thread(target=join, args=(2, 0.2, "r2-first")),
+          threading.Thread(target=join, args=(2, 0.5, "r2-second")),
+          threading.Thread(target=join, args=(1, 0.8, "r1"))]
+    [t.start() for t in ts]
+    [t.join(20) for t in ts]
+    assert [w for w, _ in zombie] == ["r2-first"]
+    assert got == {"r0": 2, "r2-second": 2, "r1": 2}
+
+
+def test_same_named_job_with_a_new_uid_never_sees_the_old_jobs_keys(srv):
+    c = RendezvousClient(srv.addr)
+    c.set("ns/job/uid-old/comm0/g0/ipc/0", b"stale")
+    with pytest.raises(TimeoutError):
+        c.get("ns/job/uid-new/comm0/g0/ipc/0", timeout=0.2)
+    g = _run([lambda r=r: RendezvousClient(srv.addr).join("ns/job/uid-new/comm0", r, 2)
+              for r in range(2)])
+    assert g == [0, 0]
+
+
+def test_descriptor_broker_passes_an_open_file_between_processes(srv, tmp_path):
+    """SCM_RIGHTS through the broker: what carries the multicast (NVLS) handle from the rank that
+    created it to the ranks that import it."""
+    r, w = os.pipe()
+    a = RendezvousClient(srv.addr, uds_path=srv.uds_path)
+    a.fd_put("ns/job/uid/comm0/g0/nvls/fd", w)
+    os.close(w)                                  # the broker holds its own duplicate
+    pid = os.fork()
+    if pid == 0:                                 # "another replica"
+        try:
+            b = RendezvousClient(srv.addr, uds_path=srv.uds_path)
+            fd = b.fd_get("ns/job/uid/comm0/g0/nvls/fd", timeout=5)
+            os.write(fd, b"through the broker")
+            os.close(fd)
+            os._exit(0)
+        except BaseException:  # noqa: BLE001
+            os._exit(1)
+    _, status = os.waitpid(pid, 0)
+    assert status == 0
+    assert os.read(r, 64) == b"through the broker"
+    os.close(r)
+    with pytest.raises(TimeoutError):
+        a.fd_get("ns/job/uid/comm0/g0/nvls/missing", timeout=0.2)
+    assert srv.delete_prefix("ns/job/uid/") == 1
+    with pytest.raises(TimeoutError):
+        a.fd_get("ns/job/uid/comm0/g0/nvls/fd", timeout=0.2)
+
+
+def test_deleting_the_job_object_clears_its_rendezvous_state():
+    from tf_operator_b200.cluster import LocalCluster
+    job = {"apiVersion": "kubeflow.org/v1", "kind": "PyTorchJob",
+           "metadata": {"name": "rdv-clean", "namespace": "default"},
+           "spec": {"pytorchReplicaSpecs": {"Master": {"replicas": 1, "restartPolicy": "Never", "template": {
+               "spec": {"containers": [{"name": "pytorch", "image": "x",
+                                        "command": ["python", "-c", "import time; time.sleep(30)"]}]}}}}}}
+    with LocalCluster() as c:
+        created = c.store.create("pytorchjobs", job)
+        uid = created["metadata"]["uid"]
+        cli = RendezvousClient(c.rendezvous.addr)
+        scope = f"default/rdv-clean/{uid}/comm0"
+        assert cli.join(scope, 0, 1) == 0
+        cli.set(f"{scope}/g0/ipc/0", b"h")
+        cli.set("default/other-job/uid-x/comm0/g0/ipc/0", b"keep")
+        # the replica's environment carries the job uid the scope is built from
+        deadline = time.time() + 10
+        pods = []
+        while time.time() < deadline and not pods:
+            pods = [p for p in c.store.list("pods") if p["metadata"]["name"] == "rdv-clean-master-0"
+                    and (p.get("status") or {}).get("phase") == "Running"]
+            time.sleep(0.05)
+        assert pods
+        env = c.kubelet._env_for(c.kubelet._pods[("default", "rdv-clean-master-0")], pods[0],
+                                 pods[0]["spec"]["containers"][0])
+        assert env["TFOP_JOB_UID"] == uid and env["TFOP_INCARNATION"] == "0"
+        assert env["TFOP_RENDEZVOUS_UDS"] == c.rendezvous.uds_path
+        c.store.delete("pytorchjobs", "default", "rdv-clean")
+        deadline = time.time() + 5
+        while time.time() < deadline and c.rendezvous.keys(f"default/rdv-clean/{uid}/"):
+            time.sleep(0.05)
+        assert c.rendezvous.keys(f"default/rdv-clean/{uid}/") == []
+        assert c.rendezvous.keys("default/other-job/") == ["default/other-job/uid-x/comm0/g0/ipc/0"]
+        # a second job of the same name gets a different uid -> a different scope
+        again = c.store.create("pytorchjobs", job)
+        assert again["metadata"]["uid"] != uid

@@ -37,6 +37,7 @@ class LocalCluster:
         if topology is not None:
             kopt.topology = topology
         kopt.rendezvous_addr = self.rendezvous.addr
+        kopt.rendezvous_uds = self.rendezvous.uds_path
         self.kubelet = LocalKubelet(self.store, kopt)
         self.manager = Manager(self.store, manager_options or ManagerOptions())
         self.api: Optional[ApiServer] = ApiServer(self.store, self.kubelet, port=http_port) \
@@ -58,9 +59,20 @@ class LocalCluster:
                          "versions": [{"name": "v1", "served": True, "storage": True,
                                        "subresources": {"status": {}}}]}})
 
+    def _on_store_event(self, resource: str, etype: str, obj) -> None:
+        # a deleted job takes its rendezvous state with it: keys, generations, brokered fds all
+        # live under <namespace>/<job>/<uid>/ (launcher/rendezvous.py)
+        if etype == "DELETED" and resource in self._job_plurals:
+            md = obj.get("metadata") or {}
+            self.rendezvous.delete_prefix(
+                f"{md.get('namespace', 'default')}/{md.get('name')}/{md.get('uid', '')}/")
+
     def start(self) -> "LocalCluster":
         if self.running:
             return self
+        from .api import KINDS
+        self._job_plurals = {m.INFO.plural for m in KINDS.values()}
+        self.store.add_listener(self._on_store_event)
         self.rendezvous.start()
         if self.api is not None:
             self.api.start()
@@ -77,6 +89,7 @@ class LocalCluster:
         self.kubelet.stop()
         if self.api is not None:
             self.api.stop()
+        self.store.remove_listener(self._on_store_event)
         self.rendezvous.stop()
         self.running = False
 

@@ -26,7 +26,10 @@
 namespace {
 
 constexpr int kThreads = 512;
-constexpr long long kSpinTimeoutCycles = 30LL * 1000 * 1000 * 1000;  // ~15 s
+// How long a block waits for a peer's flag before it gives up (SM clock cycles). Generous by
+// default - a legitimate skew of many seconds exists (a checkpoint save on one rank, a first
+// step's autotuning, an input stall) - and configurable: tfop_comm_set_timeout_ms().
+long long g_spin_timeout_cycles = 240LL * 1000 * 1000 * 1000;  // ~2 minutes at 1.9 GHz
 
 struct ARArgs {
     void* data[TFOP_MAX_WORLD];
@@ -43,6 +46,7 @@ struct ARArgs {
     int in_dtype;
     int out_dtype;
     int algo;            // 1 one-shot, 2 two-shot
+    long long timeout;   // spin limit of the flag barriers, in cycles
 };
 
 struct ARArgsEmu {
@@ -80,8 +84,15 @@ struct Wire<float> {
 // K8: block-granular flag barrier across ranks. Block b of every rank
 // rendezvous with block b of every other rank. `gen` increases by one per
 // kernel launch, so flags never need resetting.
+// Returns false when a peer never arrived (or an earlier barrier of this communicator already
+// timed out): the caller then ABANDONS the collective - no reduce, no stores - so a dead or
+// wedged peer can never turn into silently wrong gradients. The error word stays set; the
+// engine polls it and fails the replica with a retryable exit code (parallel/engine.py).
 template <int W>
-__device__ __forceinline__ void rank_barrier(const ARArgs& a, int phase, uint32_t gen) {
+__device__ __forceinline__ bool rank_barrier(const ARArgs& a, int phase, uint32_t gen) {
+    __shared__ int s_ok;
+    __syncthreads();
+    if (threadIdx.x == 0) s_ok = 1;
     __syncthreads();
     if (threadIdx.x < W) {
         const int slot = (phase * TFOP_MAX_BLOCKS + blockIdx.x) * TFOP_MAX_WORLD;
@@ -89,14 +100,19 @@ __device__ __forceinline__ void rank_barrier(const ARArgs& a, int phase, uint32_
         st_release_sys_u32(a.sig[threadIdx.x] + slot + a.rank, gen);
         const uint32_t* mine = a.sig[a.rank] + slot + threadIdx.x;
         const long long t0 = clock64();
+        unsigned spins = 0;
         while ((int32_t)(ld_acquire_sys_u32(mine) - gen) < 0) {
-            if (clock64() - t0 > kSpinTimeoutCycles) {
+            // a barrier that timed out anywhere on this rank poisons the rest quickly
+            if (clock64() - t0 > a.timeout ||
+                ((++spins & 0x3ffu) == 0 && *(volatile uint32_t*)a.err != 0u)) {
                 atomicExch(a.err, 1u);
+                s_ok = 0;
                 break;
             }
         }
     }
     __syncthreads();
+    return s_ok != 0;
 }
 
 template <typename T, int W>
@@ -142,7 +158,7 @@ __device__ void allreduce_body(const ARArgs& a) {
                 *reinterpret_cast<uint4*>(stage + v * 16) = Wire<T>::pack(f);
             }
         }
-        rank_barrier<W>(a, 0, gen);
+        if (!rank_barrier<W>(a, 0, gen)) return;
         for (size_t v = tid; v < total_vecs; v += nthreads) {
             float acc[VEC];
             reduce_vec<T, W>(a, off + v * 16, a.scale, acc);
@@ -150,7 +166,7 @@ __device__ void allreduce_body(const ARArgs& a) {
         }
         // staged input is double-buffered by parity, so no trailing barrier is
         // needed; reading user-owned symmetric memory in place needs one.
-        if (!a.in) rank_barrier<W>(a, 1, gen);
+        if (!a.in && !rank_barrier<W>(a, 1, gen)) return;
     } else {
         // ---------------- two-shot ----------------
         const size_t off = a.sym_off;
@@ -167,7 +183,7 @@ __device__ void allreduce_body(const ARArgs& a) {
                     *reinterpret_cast<uint4*>(self + v * 16) = Wire<T>::pack(f);
                 }
         }
-        rank_barrier<W>(a, 0, gen);
+        if (!rank_barrier<W>(a, 0, gen)) return;
         {
             const size_t lo = (size_t)a.rank * chunk_vecs;
             for (size_t j = tid; j < chunk_vecs; j += nthreads) {
@@ -180,7 +196,7 @@ __device__ void allreduce_body(const ARArgs& a) {
                 for (int p = 0; p < W; ++p) st_peer_v4((char*)a.data[p] + off + v * 16, pk);
             }
         }
-        rank_barrier<W>(a, 1, gen);
+        if (!rank_barrier<W>(a, 1, gen)) return;
         if (a.out) {
 #pragma unroll 1
             for (int c = 0; c < W; ++c)
@@ -248,6 +264,7 @@ int fill_args(tfop_comm* c, ARArgs* a, const void* in, int in_dtype, void* out, 
     a->in_dtype = in_dtype;
     a->out_dtype = out_dtype;
     a->algo = algo;
+    a->timeout = g_spin_timeout_cycles;
     return 0;
 }
 
@@ -346,6 +363,25 @@ TFOP_API int tfop_allreduce_emulated(tfop_comm** comms, int world, const void* c
     if (rc != 0) return rc;
     TFOP_CUDA(cudaGetLastError());
     return 0;
+}
+
+// Library-internal: the spin limit every flag barrier of this library uses (nvls.cu too).
+long long tfop_spin_timeout_cycles() { return g_spin_timeout_cycles; }
+
+// Spin limit of the cross-rank flag barriers, in milliseconds of a 2 GHz SM clock (default
+// 120,000). When it expires the kernel abandons the collective and sets the communicator's
+// error word. Applies to calls issued (or graphs captured) afterwards.
+TFOP_API int tfop_comm_set_timeout_ms(long long ms) {
+    TFOP_REQUIRE(ms > 0, "timeout must be positive");
+    g_spin_timeout_cycles = ms * 2000000LL;
+    return 0;
+}
+
+// Device address of the communicator's error word (uint32: 0 = healthy), for callers that copy
+// it to the host asynchronously next to their own results instead of calling
+// tfop_comm_check_error, which synchronises.
+TFOP_API void* tfop_comm_error_ptr(tfop_comm* c) {
+    return c ? (void*)(c->sig[c->rank] + TFOP_SIG_WORDS) : nullptr;
 }
 
 // Returns 1 if any barrier of this communicator ever timed out (a peer died).

@@ -24,4 +24,5 @@ struct tfop_comm {
     void* mc_ptr;                    // multicast VA covering the data buffer (or null)
     void* mc_uc_ptr;                 // local unicast VA of the multicast-bound memory
     size_t mc_bytes;
+    int quiesced;                    // set by tfop_comm_quiesce(): peers are done with our buffers
 };

@@ -24,6 +24,8 @@
 #include <cuda.h>
 #include <unistd.h>
 
+long long tfop_spin_timeout_cycles();  // allreduce.cu (library-internal)
+
 namespace {
 
 // ---- driver entry points (no link-time dependency on libcuda) --------------------------
@@ -110,7 +112,6 @@ CUmulticastObjectProp mc_prop(int world, size_t bytes) {
 
 // ---- device side --------------------------------------------------------------------------
 constexpr int kThreads = 512;
-constexpr long long kSpinTimeoutCycles = 30LL * 1000 * 1000 * 1000;
 
 struct NvlsArgs {
     uint32_t* sig[TFOP_MAX_WORLD];
@@ -124,9 +125,14 @@ struct NvlsArgs {
     float scale;
     int rank, world;
     int in_dtype, out_dtype;
+    long long timeout;     // spin limit of the flag barriers (tfop_comm_set_timeout_ms)
 };
 
-__device__ __forceinline__ void nvls_barrier(const NvlsArgs& a, int phase, uint32_t gen) {
+// false = a peer never arrived: the caller abandons the collective (see allreduce.cu).
+__device__ __forceinline__ bool nvls_barrier(const NvlsArgs& a, int phase, uint32_t gen) {
+    __shared__ int s_ok;
+    __syncthreads();
+    if (threadIdx.x == 0) s_ok = 1;
     __syncthreads();
     if ((int)threadIdx.x < a.world) {
         const int slot = (phase * TFOP_MAX_BLOCKS + blockIdx.x) * TFOP_MAX_WORLD;
@@ -134,14 +140,18 @@ __device__ __forceinline__ void nvls_barrier(const NvlsArgs& a, int phase, uint3
         st_release_sys_u32(a.sig[threadIdx.x] + slot + a.rank, gen);
         const uint32_t* mine = a.sig[a.rank] + slot + threadIdx.x;
         const long long t0 = clock64();
+        unsigned spins = 0;
         while ((int32_t)(ld_acquire_sys_u32(mine) - gen) < 0) {
-            if (clock64() - t0 > kSpinTimeoutCycles) {
+            if (clock64() - t0 > a.timeout ||
+                ((++spins & 0x3ffu) == 0 && *(volatile uint32_t*)a.err != 0u)) {
                 atomicExch(a.err, 1u);
+                s_ok = 0;
                 break;
             }
         }
     }
     __syncthreads();
+    return s_ok != 0;
 }
 
 // 16 bytes through the switch: sum over all ranks' copies (fp32 accumulation for bf16)
@@ -199,7 +209,7 @@ __global__ void __launch_bounds__(kThreads) nvls_allreduce_kernel(const NvlsArgs
                 *reinterpret_cast<uint4*>(a.uc + v * 16) = pk;
             }
     }
-    nvls_barrier(a, 2, gen);
+    if (!nvls_barrier(a, 2, gen)) return;
     // in-switch reduce of my chunk, scale, broadcast to every rank's copy
     {
         const size_t lo = (size_t)a.rank * chunk_vecs;
@@ -225,7 +235,7 @@ __global__ void __launch_bounds__(kThreads) nvls_allreduce_kernel(const NvlsArgs
             mm_st_v4(a.mc + v * 16, r);
         }
     }
-    nvls_barrier(a, 3, gen);
+    if (!nvls_barrier(a, 3, gen)) return;
     if (a.out) {
         for (int c = 0; c < a.world; ++c)
             for (size_t j = tid; j < chunk_vecs; j += nthreads) {
@@ -392,6 +402,7 @@ TFOP_API int tfop_allreduce_nvls(tfop_comm* c, const void* in, int in_dtype, voi
     a.world = c->world;
     a.in_dtype = in_dtype;
     a.out_dtype = out_dtype;
+    a.timeout = tfop_spin_timeout_cycles();
     const size_t total_vecs = (n + vec - 1) / vec;
     const size_t work = (total_vecs + c->world - 1) / c->world;
     if (max_blocks <= 0 || max_blocks > TFOP_MAX_BLOCKS) max_blocks = TFOP_MAX_BLOCKS;

@@ -77,8 +77,9 @@ __global__ void __launch_bounds__(256) adamw_kernel(
     const float* __restrict__ hp) {
     const float lr = hp[HP_LR], wd = hp[HP_WD], gs = hp[HP_GSCALE];
     const float b1 = hp[HP_B1], b2 = hp[HP_B2], eps = hp[HP_EPS], step = hp[HP_STEP];
-    const float c1 = 1.f / (1.f - __powf(b1, step));
-    const float c2 = 1.f / (1.f - __powf(b2, step));
+    // -expm1(step * log(beta)) = 1 - beta^step without cancellation (beta2 = 0.999: 1e-3 at step 1)
+    const float c1 = -1.f / expm1f(step * logf(b1));
+    const float c2 = -1.f / expm1f(step * logf(b2));
     const float omb1 = 1.f - b1, omb2 = 1.f - b2;
     const size_t nv = n / 4;
     const size_t stride = (size_t)gridDim.x * blockDim.x;

@@ -113,8 +113,23 @@ TFOP_API size_t tfop_comm_buffer_bytes(tfop_comm* c) { return c->data_bytes; }
 TFOP_API int tfop_comm_rank(tfop_comm* c) { return c->rank; }
 TFOP_API int tfop_comm_world(tfop_comm* c) { return c->world; }
 
+// The caller states that every peer has finished with this rank's buffers (it ran a cross-rank
+// exit barrier after its last collective). Until then tfop_comm_destroy refuses to free.
+TFOP_API int tfop_comm_quiesce(tfop_comm* c) {
+    TFOP_REQUIRE(c != nullptr, "null comm");
+    c->quiesced = 1;
+    return 0;
+}
+
+// Frees the local buffers and unmaps the peers'. With peers (world > 1, real IPC mappings) the
+// memory may still be read or written by their kernels over NVLink: freeing it under them is a
+// fault on THEIR side. So destroy only proceeds after tfop_comm_quiesce(); otherwise it returns
+// an error and leaves everything mapped (process exit reclaims it).
 TFOP_API int tfop_comm_destroy(tfop_comm* c) {
     if (!c) return 0;
+    TFOP_REQUIRE(c->world == 1 || c->emulated || c->quiesced,
+                 "peers may still be using this rank's symmetric buffers: run an exit barrier "
+                 "across the ranks, call tfop_comm_quiesce(), then destroy");
     cudaDeviceSynchronize();
     for (int p = 0; p < c->world; ++p) {
         if (p == c->rank) continue;

@@ -51,6 +51,7 @@ class KubeletOptions:
     gpus_per_replica_default: int = 0       # GPUs for pods that do not ask for nvidia.com/gpu
     topology: Optional[Topology] = None
     rendezvous_addr: str = ""               # exported as TFOP_RENDEZVOUS
+    rendezvous_uds: str = ""                # descriptor broker socket, TFOP_RENDEZVOUS_UDS
     extra_env: Dict[str, str] = field(default_factory=dict)
     python: str = sys.executable
     cwd: str = ""
@@ -259,9 +260,20 @@ class LocalKubelet:
             "TFOP_REPLICA_TYPE": labels.get(c.LABEL_REPLICA_TYPE, ""),
             "TFOP_REPLICA_INDEX": labels.get(c.LABEL_REPLICA_INDEX, ""),
             "TFOP_GPU_COUNT": str(len(rt.gpus)),
+            # identity of this incarnation: the owning job's uid scopes every rendezvous key (a
+            # re-created job of the same name starts clean); pod uid + restart count tell a
+            # restarted replica apart from the process it replaces
+            "TFOP_JOB_UID": next((o.get("uid", "") for o in
+                                  pod["metadata"].get("ownerReferences") or []
+                                  if o.get("controller")), ""),
+            "TFOP_POD_UID": str(rt.uid or ""),
+            "TFOP_INCARNATION": str(rt.containers[ctr["name"]].restart_count
+                                    if ctr["name"] in rt.containers else 0),
         })
         if self.opt.rendezvous_addr:
             env["TFOP_RENDEZVOUS"] = self.opt.rendezvous_addr
+        if self.opt.rendezvous_uds:
+            env["TFOP_RENDEZVOUS_UDS"] = self.opt.rendezvous_uds
         if rt.gpus:
             env["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in rt.gpus)
         elif self.topology.count and self._gpus_wanted(pod) == 0 and \

@@ -31,6 +31,9 @@ _SIGS = {
     "tfop_comm_world": (c_int, [c_void_p]),
     "tfop_comm_check_error": (c_int, [c_void_p, C.POINTER(c_int)]),
     "tfop_comm_destroy": (c_int, [c_void_p]),
+    "tfop_comm_quiesce": (c_int, [c_void_p]),
+    "tfop_comm_set_timeout_ms": (c_int, [C.c_longlong]),
+    "tfop_comm_error_ptr": (c_void_p, [c_void_p]),
     "tfop_allreduce": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_size_t,
                                c_size_t, c_float, c_int, c_int, c_void_p]),
     "tfop_allreduce_emulated": (c_int, [C.POINTER(c_void_p), c_int, C.POINTER(c_void_p), c_int,

@@ -27,18 +27,24 @@ import torch.nn.functional as F
 
 from ..ops import optim as fopt
 from ..ops import preproc
-from ..runtime.symm import SymmetricComm, TWO_SHOT
+from ..runtime.symm import CommError, SymmetricComm, TWO_SHOT
 from .flat import FlatParams
 
 
 class StepHandle:
     """Result of an asynchronous step; ``result()`` is the device->host read."""
 
-    def __init__(self, host_loss: torch.Tensor, event: torch.cuda.Event):
-        self._host, self._event = host_loss, event
+    def __init__(self, host_loss: torch.Tensor, event: torch.cuda.Event,
+                 host_err: Optional[torch.Tensor] = None):
+        self._host, self._event, self._err = host_loss, event, host_err
 
     def result(self) -> float:
         self._event.synchronize()
+        if self._err is not None and int(self._err.item()) != 0:
+            # the gradient exchange of this step gave up on a peer and reduced nothing: the
+            # optimizer then stepped on this rank's own gradient only. Stop here and let the
+            # operator restart the gang from the last checkpoint.
+            raise CommError("gradient all-reduce timed out waiting for a peer replica")
         return float(self._host.item())
 
 
@@ -80,10 +86,19 @@ class FlatDataParallel:
         self.mom2 = torch.zeros(self.flat.total, dtype=torch.float32, device=self.device) \
             if optimizer == "adamw" else None
         self.hp = torch.zeros(8, dtype=torch.float32, device=self.device)
+        # The H2D copy of the hyper-parameters reads host memory when the copy EXECUTES, and an
+        # eager host runs steps ahead of the GPU: each upload gets its own pinned buffer out of
+        # a ring, reused only after the copy that read it has completed.
         self._hp_host = torch.tensor([lr, momentum, weight_decay, 1.0, betas[0], betas[1], eps, 0.0],
                                      dtype=torch.float32).pin_memory()
+        self._hp_ring = [(torch.empty(8, dtype=torch.float32).pin_memory(), torch.cuda.Event())
+                         for _ in range(4)]
+        self._hp_next = 0
         self.hp.copy_(self._hp_host)
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        # eager engines poll the communicator's error word every this many steps (and at every
+        # checkpoint); DataParallelEngine reads it back with each step's loss instead
+        self.check_comm_every = 50
         self.kernel_launches_per_step = 0
         self._steps = 0
         self._in_backward = False
@@ -167,17 +182,29 @@ class FlatDataParallel:
         l0 = _lib.launches_total()
         if self.optimizer == "adamw":
             self._hp_host[7] = float(self._steps + 1)
-            self.hp.copy_(self._hp_host, non_blocking=True)
+            self._upload_hp()
         self._begin()
         loss = closure()
         self._backward_and_update(loss)
         self.kernel_launches_per_step = _lib.launches_total() - l0
         self._steps += 1
+        if self.comm is not None and self._steps % self.check_comm_every == 0:
+            self.comm.raise_if_failed()          # synchronises: amortised over many steps
         return loss.detach()
+
+    def _upload_hp(self, stream=None):
+        buf, ev = self._hp_ring[self._hp_next]
+        self._hp_next = (self._hp_next + 1) % len(self._hp_ring)
+        ev.synchronize()                      # no-op until the ring wraps around a busy slot
+        buf.copy_(self._hp_host)
+        st = stream or torch.cuda.current_stream()
+        with torch.cuda.stream(st):
+            self.hp.copy_(buf, non_blocking=True)
+            ev.record(st)
 
     def set_lr(self, lr: float):
         self._hp_host[0] = lr
-        self.hp.copy_(self._hp_host, non_blocking=True)
+        self._upload_hp()
 
     # ------------------------------------------------------------------ checkpoint / resume
     # The reference operator never touches model state: resume works by
@@ -190,6 +217,8 @@ class FlatDataParallel:
         buffers, hyper-parameters and the step counter. ``sd["model"]`` loads into the plain
         ``nn.Module`` with ``load_state_dict(..., strict=False)``."""
         torch.cuda.current_stream().synchronize()
+        if self.comm is not None:
+            self.comm.raise_if_failed()          # never persist weights a dead peer starved
         sd = {"version": 1, "optimizer": self.optimizer, "step": int(self._steps),
               "hp": [float(x) for x in self._hp_host.tolist()],
               "model": self.flat.export_named(self.flat.master),
@@ -264,6 +293,8 @@ class DataParallelEngine(FlatDataParallel):
         self._stage_ready = [torch.cuda.Event() for _ in range(2)]
         self._stage_free = [torch.cuda.Event() for _ in range(2)]
         self._host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self._host_err = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(2)] \
+            if comm is not None else None
         self._slot = 0
         self._prefetched = None
         self.copy_stream = torch.cuda.Stream(device=self.device)
@@ -342,23 +373,25 @@ class DataParallelEngine(FlatDataParallel):
             self._stage_free[slot].record(ms)
         self.run_device_step()
         host = self._host_loss[self._steps & 1]
+        herr = self._host_err[self._steps & 1] if self._host_err is not None else None
         ev = torch.cuda.Event()
         with torch.cuda.stream(ms):
             host.copy_(self.loss_dev, non_blocking=True)
+            if herr is not None:
+                herr.copy_(self.comm.error_word(), non_blocking=True)
             ev.record(ms)
-        return StepHandle(host, ev)
+        return StepHandle(host, ev, herr)
 
     # ------------------------------------------------------------------ misc
     def set_lr(self, lr: float):
         self._hp_host[0] = lr
-        with torch.cuda.stream(self.main_stream):
-            self.hp.copy_(self._hp_host, non_blocking=True)
+        self._upload_hp(self.main_stream)
 
     def h2d_bytes_per_step(self) -> int:
         return self.x_u8.numel() + self.labels.numel() * 8
 
     def d2h_bytes_per_step(self) -> int:
-        return 4
+        return 4 + (4 if self._host_err is not None else 0)
 
     def synchronize(self):
         torch.cuda.synchronize(self.device)

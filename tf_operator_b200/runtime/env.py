@@ -134,28 +134,42 @@ class ReplicaContext:
         """Symmetric peer-memory communicator; handles are exchanged through the launcher's
         rendezvous store when there is one, else through torch.distributed. ``nvls_bytes`` > 0
         additionally binds a multicast (NVLS) buffer of that size when the box supports it
-        (``comm.nvls_bytes`` is 0 otherwise)."""
+        (``comm.nvls_bytes`` is 0 otherwise); under the launcher the multicast descriptor goes
+        through its broker too, so no torch.distributed group is created."""
         comm = self._symmetric_comm(nbytes, tag)
         comm.nvls_bytes = 0
         if nvls_bytes and self.world_size > 1:
-            import torch.distributed as dist
-            if not dist.is_initialized():
-                self.init_process_group("gloo")
+            if getattr(comm, "_rdv", None) is None:
+                import torch.distributed as dist
+                if not dist.is_initialized():
+                    self.init_process_group("gloo")
             comm.enable_nvls(nvls_bytes)
         return comm
+
+    def rendezvous_scope(self, tag: str) -> str:
+        """``<namespace>/<job>/<job uid>/<tag>``: the uid (TFOP_JOB_UID, exported by the launcher)
+        keeps a re-created job of the same name away from its predecessor's keys."""
+        return f"{self.namespace}/{self.job_name}/{self.raw.get('TFOP_JOB_UID', '')}/{tag}"
 
     def _symmetric_comm(self, nbytes: int, tag: str):
         from .symm import SymmetricComm
         addr = self.raw.get("TFOP_RENDEZVOUS")
         if addr and self.world_size > 1:
             from ..launcher.rendezvous import RendezvousClient
-            cli = RendezvousClient(addr)
-            prefix = f"{self.namespace}/{self.job_name}/{tag}"
+            cli = RendezvousClient(addr, uds_path=self.raw.get("TFOP_RENDEZVOUS_UDS", ""))
+            # join the gang's current generation (a restarted replica opens a new one, its peers
+            # follow once their collectives have timed out and the operator has restarted them)
+            scope = self.rendezvous_scope(tag)
+            gen = cli.join(scope, self.rank, self.world_size)
+            prefix = f"{scope}/g{gen}"
             comm = SymmetricComm.create(
                 self.rank, self.world_size, nbytes,
                 lambda b: cli.all_gather(prefix + "/ipc", self.rank, self.world_size, b))
             cli.barrier(prefix + "/ready", self.world_size)
-            cli.close()
+            comm._rdv = (cli, prefix)
+            comm.generation = gen
+            world = self.world_size
+            comm._exit_barrier = lambda: cli.barrier(prefix + "/exit", world, timeout=60)
             return comm
         if self.world_size > 1:
             return SymmetricComm.from_torch_distributed(nbytes)

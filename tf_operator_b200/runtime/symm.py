@@ -20,6 +20,19 @@ from ..ops import _lib
 
 AUTO, ONE_SHOT, TWO_SHOT = 0, 1, 2
 
+# Exit code of a replica whose collective gave up on a peer. 138 (= 128 + SIGUSR1) is the
+# "user-defined retryable" code of the operator's ExitCode restart policy
+# (train_util.IsRetryableExitCode): the operator re-creates the replica, and
+# because every surviving rank hits the same timeout, the whole gang re-forms.
+RETRYABLE_EXIT_CODE = 138
+
+
+class CommError(RuntimeError):
+    """A cross-rank barrier of a collective timed out: a peer is dead or wedged. The collective
+    was abandoned (no data was reduced or stored); the replica should exit with
+    ``RETRYABLE_EXIT_CODE`` so the operator restarts it."""
+    exit_code = RETRYABLE_EXIT_CODE
+
 
 class _RawCudaBuffer:
     """Expose a raw device pointer to torch through __cuda_array_interface__."""
@@ -78,6 +91,7 @@ class SymmetricComm:
 
         comm = cls.create(rank, world, nbytes, exchange)
         dist.barrier(group=group)
+        comm._exit_barrier = lambda: dist.barrier(group=group)
         return comm
 
     @classmethod
@@ -128,8 +142,16 @@ class SymmetricComm:
 
     def enable_nvls(self, nbytes: int, group=None) -> bool:
         """Create/import the multicast object, bind this rank's memory and map both views.
-        The multicast fd travels from rank 0 to the others over a Unix socket (SCM_RIGHTS);
-        torch.distributed provides the barriers. Returns False when the box has no NVLS."""
+        Returns False when the box has no NVLS.
+
+        A communicator that was formed through the launcher's rendezvous store (``_rdv`` set by
+        ReplicaContext.symmetric_comm) passes the multicast file descriptor through the
+        launcher's descriptor broker (SCM_RIGHTS over its Unix socket) and barriers on the store:
+        no torch.distributed process group is needed. Otherwise (torchrun-style launches) the
+        descriptor travels from rank 0 over an ad-hoc Unix socket and torch.distributed provides
+        the barriers."""
+        if getattr(self, "_rdv", None) is not None and group is None:
+            return self._enable_nvls_brokered(nbytes)
         import os
         import socket
         import time
@@ -185,6 +207,43 @@ class SymmetricComm:
             dist.barrier(group=group)
             _lib.check(lib.tfop_nvls_bind(self._h), "nvls_bind")
             dist.barrier(group=group)
+        self.nvls_bytes = lib.tfop_nvls_bytes(self._h)
+        return True
+
+    def _enable_nvls_brokered(self, nbytes: int) -> bool:
+        import os
+        cli, prefix = self._rdv
+        self.nvls_bytes = 0
+        if self.world == 1:
+            return False
+        lib, base = self._lib, f"{prefix}/nvls"
+        ok = self.nvls_supported()
+        with torch.cuda.device(self.device):
+            if self.rank == 0:
+                fd = C.c_int(-1)
+                if ok and lib.tfop_nvls_create(self._h, nbytes, C.byref(fd)) == 0:
+                    cli.fd_put(f"{base}/fd", fd.value)       # the broker keeps its own duplicate
+                    os.close(fd.value)
+                else:
+                    ok = False
+                cli.set(f"{base}/created", b"1" if ok else b"0")
+            else:
+                if cli.get(f"{base}/created") != b"1":
+                    ok = False
+                elif ok:
+                    fd = cli.fd_get(f"{base}/fd")
+                    try:
+                        ok = lib.tfop_nvls_import(self._h, nbytes, fd) == 0
+                    finally:
+                        os.close(fd)
+            # every rank must have the object before any binds; all or nothing
+            votes = cli.all_gather(f"{base}/ok", self.rank, self.world, b"1" if ok else b"0")
+            if any(v != b"1" for v in votes):
+                return False
+            _lib.check(lib.tfop_nvls_add_device(self._h), "nvls_add_device")
+            cli.barrier(f"{base}/added", self.world)
+            _lib.check(lib.tfop_nvls_bind(self._h), "nvls_bind")
+            cli.barrier(f"{base}/bound", self.world)
         self.nvls_bytes = lib.tfop_nvls_bytes(self._h)
         return True
 
@@ -245,18 +304,51 @@ class SymmetricComm:
         flat = self.nvls_view((m - 1) * ldo + n, torch.bfloat16, out_off)
         return torch.as_strided(flat, (m, n), (ldo, 1))
 
+    def set_timeout_ms(self, ms: int) -> None:
+        """Spin limit of the flag barriers (default 120 s). Process-wide; applies to collectives
+        issued or captured afterwards."""
+        _lib.check(self._lib.tfop_comm_set_timeout_ms(int(ms)), "comm_set_timeout_ms")
+
+    def error_word(self) -> torch.Tensor:
+        """int32 device tensor aliasing the communicator's error word (0 = healthy): copy it to
+        pinned host memory next to a step's loss to learn about a timed-out barrier without a
+        synchronising call."""
+        if "err" not in self._views:
+            p = self._lib.tfop_comm_error_ptr(self._h)
+            self._views["err"] = tensor_from_ptr(p, 4, self.device, owner=self).view(torch.int32)
+        return self._views["err"]
+
+    def raise_if_failed(self) -> None:
+        if self.check_error():
+            raise CommError(f"rank {self.rank}: a collective timed out waiting for a peer")
+
     def check_error(self) -> bool:
         flag = C.c_int(0)
         _lib.check(self._lib.tfop_comm_check_error(self._h, C.byref(flag)), "comm_check_error")
         return bool(flag.value)
 
-    def close(self):
-        if self._h:
-            self._views.clear()
-            if getattr(self, "nvls_bytes", 0):
-                self._lib.tfop_nvls_destroy(self._h)
-            self._lib.tfop_comm_destroy(self._h)
-            self._h = None
+    def close(self, exit_barrier: Optional[Callable[[], None]] = None) -> bool:
+        """Release the buffers. With peers, their kernels may still be reading this rank's memory
+        over NVLink, so the ranks must first agree that they are all done: ``exit_barrier`` (or
+        the one the communicator was formed with - the launcher's rendezvous store or the
+        torch.distributed group) runs after a device synchronise, and only then is the memory
+        freed. Without any barrier the buffers stay mapped until the process exits (returns
+        False) - never freed under a peer."""
+        if not self._h:
+            return True
+        torch.cuda.synchronize(self.device)
+        barrier = exit_barrier or getattr(self, "_exit_barrier", None)
+        if self.world > 1 and not self.emulated:
+            if barrier is None:
+                return False
+            barrier()
+            self._lib.tfop_comm_quiesce(self._h)
+        self._views.clear()
+        if getattr(self, "nvls_bytes", 0):
+            self._lib.tfop_nvls_destroy(self._h)
+        _lib.check(self._lib.tfop_comm_destroy(self._h), "comm_destroy")
+        self._h = None
+        return True
 
 
 def all_reduce_emulated(comms: Sequence[SymmetricComm], n: int, *,
