@@ -12,6 +12,8 @@ L3-L5): kube-apiserver (store/), the operator Deployment (operator/), kubelet + 
 """
 from __future__ import annotations
 
+import itertools
+import os
 import threading
 from typing import Optional
 
@@ -23,6 +25,7 @@ from .store.http import ApiServer
 from .store.memory import ObjectStore
 
 _default_lock = threading.Lock()
+_cluster_seq = itertools.count(1)
 _default: Optional["LocalCluster"] = None
 
 
@@ -36,6 +39,10 @@ class LocalCluster:
         kopt = kubelet_options or KubeletOptions()
         if topology is not None:
             kopt.topology = topology
+        if not kopt.cluster_id:
+            # unique per cluster object AND per host process: pod addresses of two clusters differ
+            kopt.cluster_id = f"{os.getpid():x}-{next(_cluster_seq)}"
+        self.cluster_id = kopt.cluster_id
         kopt.rendezvous_addr = self.rendezvous.addr
         kopt.rendezvous_uds = self.rendezvous.uds_path
         self.kubelet = LocalKubelet(self.store, kopt)

@@ -493,11 +493,14 @@ TFOP_API int tfop_conv_stem_s2d_fwd(const void* x, const void* w, void* y, int n
         cuuint32_t box[4] = {kCout, kTileOW, 2, 1};
         if (encode(&my, y, 4, dims, strides, box, "y")) return -1;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};   // per device
+    int dev = 0;
+    TFOP_CUDA(cudaGetDevice(&dev));
+    TFOP_REQUIRE(dev >= 0 && dev < 64, "device index out of range");
+    if (!attr_set[dev]) {
         TFOP_CUDA(cudaFuncSetAttribute(conv_stem_fwd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     int sms = 0;
     if (tfop_gemm_num_sms(&sms) != 0) return -1;
@@ -543,11 +546,14 @@ TFOP_API int tfop_conv_stem_s2d_wgrad(const void* x, const void* dy, float* dw, 
         cuuint32_t box[4] = {kCout, kTileOW, kWgPatchOH, 1};
         if (encode(&mdy, const_cast<void*>(dy), 4, dims, strides, box, "dy")) return -1;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};   // per device
+    int dev = 0;
+    TFOP_CUDA(cudaGetDevice(&dev));
+    TFOP_REQUIRE(dev >= 0 && dev < 64, "device index out of range");
+    if (!attr_set[dev]) {
         TFOP_CUDA(cudaFuncSetAttribute(conv_stem_wgrad_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     int sms = 0;
     if (tfop_gemm_num_sms(&sms) != 0) return -1;

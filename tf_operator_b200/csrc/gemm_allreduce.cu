@@ -479,12 +479,10 @@ TFOP_API int tfop_gemm_allreduce_bf16_tn(tfop_comm* c, const void* A, const void
     CUtensorMap ma, mb;
     if (tfop_gemm_make_tensor_map(&ma, A, M, K, lda, BLOCK_M) != 0) return -1;
     if (tfop_gemm_make_tensor_map(&mb, B, N, K, ldb, BN) != 0) return -1;
-    static bool attr = false;
-    if (!attr) {
+    {   // per call: cheap, and right for whichever device is current
         TFOP_CUDA(cudaFuncSetAttribute(gemm_allreduce_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        kGarSmemBytes));
-        attr = true;
     }
     int sms = 0;
     if (tfop_gemm_num_sms(&sms) != 0) return -1;
@@ -532,11 +530,9 @@ TFOP_API int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const
     CUtensorMap ma, mb;
     if (tfop_gemm_make_tensor_map(&ma, A, M, K, lda, BLOCK_M) != 0) return -1;
     if (tfop_gemm_make_tensor_map(&mb, B, N, K, ldb, BN) != 0) return -1;
-    static bool attr = false;
-    if (!attr) {
+    {   // per call: cheap, and right for whichever device is current
         TFOP_CUDA(cudaFuncSetAttribute(gemm_allreduce_nvls_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kGarSmemBytes));
-        attr = true;
     }
     int sms = 0;
     if (tfop_gemm_num_sms(&sms) != 0) return -1;
@@ -565,12 +561,10 @@ TFOP_API int tfop_gemm_allreduce_emulated(tfop_comm** comms, int world, const vo
         if (tfop_gemm_make_tensor_map(&maps.a[r], As[r], M, K, lda, BLOCK_M) != 0) return -1;
         if (tfop_gemm_make_tensor_map(&maps.b[r], Bs[r], N, K, ldb, BN) != 0) return -1;
     }
-    static bool attr = false;
-    if (!attr) {
+    {   // per call: cheap, and right for whichever device is current
         TFOP_CUDA(cudaFuncSetAttribute(gemm_allreduce_kernel_emu,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        kGarSmemBytes));
-        attr = true;
     }
     int sms = 0;
     if (tfop_gemm_num_sms(&sms) != 0) return -1;

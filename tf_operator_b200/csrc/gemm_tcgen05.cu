@@ -539,8 +539,27 @@ int make_map_c(CUtensorMap* map, void* base, int M, int N, int ldc, int out_dtyp
     return 0;
 }
 
-int g_num_sms = 0;
+// Per-DEVICE launch state: SM count, whether the kernel instantiation's shared-memory attribute
+// has been set on that device, and how many CTAs / 2-CTA clusters fit there. A process that
+// drives several GPUs (one replica per GPU is the norm, but nothing forbids more) must not run
+// the second device with the first one's numbers or with an unset attribute.
+constexpr int kMaxDevices = 64;
+int g_num_sms_dev[kMaxDevices] = {};
 int g_force_direct_store = 0;
+
+int current_device(int* dev) {
+    TFOP_CUDA(cudaGetDevice(dev));
+    TFOP_REQUIRE(*dev >= 0 && *dev < kMaxDevices, "device index out of range");
+    return 0;
+}
+int num_sms(int* out) {
+    int dev = 0;
+    if (current_device(&dev) != 0) return -1;
+    if (g_num_sms_dev[dev] == 0)
+        TFOP_CUDA(cudaDeviceGetAttribute(&g_num_sms_dev[dev], cudaDevAttrMultiProcessorCount, dev));
+    *out = g_num_sms_dev[dev];
+    return 0;
+}
 
 int g_cluster_mode = -1;  // -1 auto, 0 off, 1 force clusters of two
 int g_group_m = 0;        // 0: default band height; > 0: override (benchmark hook)
@@ -550,10 +569,12 @@ template <int BN, bool kTmaStore, int kCluster>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, void* C,
            const void* bias, int bias_dtype, int M, int N, int K, int ldc, int out_dtype, int epi,
            int a_mn, int b_mn, int splits_req, bool can_split, cudaStream_t stream) {
-    static bool attr_set = false;
-    static int max_ctas = 0;
+    static int max_ctas_dev[kMaxDevices] = {};   // per instantiation and device; 0 = not set up
     auto kern = gemm_tn_kernel<BN, kTmaStore, kCluster>;
-    if (!attr_set) {
+    int dev = 0, g_num_sms = 0;
+    if (current_device(&dev) != 0 || num_sms(&g_num_sms) != 0) return -1;
+    int& max_ctas = max_ctas_dev[dev];
+    if (max_ctas == 0) {
         TFOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg<BN, kCluster>::kSmemBytes));
         max_ctas = g_num_sms;
@@ -575,7 +596,6 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
             TFOP_REQUIRE(n > 0, "no 2-CTA cluster of the GEMM kernel fits on this device");
             max_ctas = 2 * n;
         }
-        attr_set = true;
     }
     const int m_units = ((M + BLOCK_M - 1) / BLOCK_M + kCluster - 1) / kCluster;
     const int tiles = m_units * ((N + BN - 1) / BN);
@@ -643,15 +663,7 @@ int tfop_gemm_make_tensor_map(CUtensorMap* map, const void* base, int rows, int 
     if (get_encode() != 0) return -1;
     return make_map(map, base, rows, K, ld, box_rows);
 }
-int tfop_gemm_num_sms(int* out) {
-    if (g_num_sms == 0) {
-        int dev = 0;
-        TFOP_CUDA(cudaGetDevice(&dev));
-        TFOP_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
-    *out = g_num_sms;
-    return 0;
-}
+int tfop_gemm_num_sms(int* out) { return num_sms(out); }
 
 // C[M,N] = epi(op(A) * op(B)^T + bias[N]), bf16 operands, fp32 accumulation in TMEM.
 //   a_mn = 0: A is [M, K] row-major (K-major), lda elements between rows
@@ -674,11 +686,8 @@ TFOP_API int tfop_gemm_bf16(const void* A, const void* B, void* C, const void* b
     TFOP_REQUIRE(epilogue >= 0 && epilogue <= 4, "bad epilogue");
     TFOP_REQUIRE(epilogue == 0 || bias != nullptr, "epilogue needs a bias pointer");
     if (get_encode() != 0) return -1;
-    if (g_num_sms == 0) {
-        int dev = 0;
-        TFOP_CUDA(cudaGetDevice(&dev));
-        TFOP_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    int g_num_sms = 0;
+    if (num_sms(&g_num_sms) != 0) return -1;
     if (tile_n == 0) {
         // wide tiles when they still fill the machine
         const long tiles256 = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + 255) / 256);

@@ -52,6 +52,7 @@ class KubeletOptions:
     topology: Optional[Topology] = None
     rendezvous_addr: str = ""               # exported as TFOP_RENDEZVOUS
     rendezvous_uds: str = ""                # descriptor broker socket, TFOP_RENDEZVOUS_UDS
+    cluster_id: str = ""                    # mixed into every pod's loopback address (netmap)
     extra_env: Dict[str, str] = field(default_factory=dict)
     python: str = sys.executable
     cwd: str = ""
@@ -83,12 +84,50 @@ class _PodRuntime:
         self.lock = threading.Lock()
 
 
+class _HostGpuLocks:
+    """Host-wide claim on physical GPUs: one lock file per GPU (by UUID) under the system temp
+    directory, held with flock for as long as a pod of THIS launcher runs on it. Two operators on
+    one box (two LocalClusters, two test sessions) each keep their own free list; the lock is
+    what stops them from handing the same B200 to two replicas. Synthetic topologies (tests
+    without GPUs) take no locks."""
+
+    def __init__(self, topology: Topology):
+        self._enabled = topology.source not in ("none", "synthetic") and topology.count > 0
+        self._names = {g.index: (g.uuid or f"index-{g.index}").replace("/", "_") for g in topology.gpus}
+        self._held: Dict[int, Any] = {}
+        self._dir = Path(tempfile.gettempdir()) / "tfop-b200-gpu-locks"
+
+    def acquire(self, gpu: int) -> bool:
+        if not self._enabled or gpu in self._held:
+            return True
+        import fcntl
+        self._dir.mkdir(parents=True, exist_ok=True)
+        f = open(self._dir / f"{self._names.get(gpu, gpu)}.lock", "a+")
+        try:
+            fcntl.flock(f, fcntl.LOCK_EX | fcntl.LOCK_NB)
+        except OSError:
+            f.close()
+            return False
+        f.seek(0)
+        f.truncate()
+        f.write(f"{os.getpid()}\n")
+        f.flush()
+        self._held[gpu] = f
+        return True
+
+    def release(self, gpu: int) -> None:
+        f = self._held.pop(gpu, None)
+        if f is not None:
+            f.close()                      # closing the descriptor drops the flock
+
+
 class LocalKubelet:
     def __init__(self, store: ObjectStore, options: Optional[KubeletOptions] = None):
         self.store = store
         self.opt = options or KubeletOptions()
         self.topology = self.opt.topology if self.opt.topology is not None else probe()
         self._free_gpus = [g.index for g in self.topology.gpus]
+        self._gpu_locks = _HostGpuLocks(self.topology)
         self._pods: Dict[tuple, _PodRuntime] = {}
         self._pending_gang: Dict[tuple, Dict[str, Any]] = {}
         self._lock = threading.RLock()
@@ -198,7 +237,7 @@ class LocalKubelet:
         with self._lock:
             for pod in pods:
                 want = self._gpus_wanted(pod)
-                gpus = self.topology.pick(want, self._free_gpus) if want else []
+                gpus = self._claim_gpus(want) if want else []
                 if gpus is None:
                     self._fail_unschedulable(pod, f"Insufficient {GPU_RESOURCE}: want {want}, "
                                                   f"free {len(self._free_gpus)}")
@@ -211,6 +250,25 @@ class LocalKubelet:
                 self._pods[(rt.ns, rt.name)] = rt
                 threading.Thread(target=self._run_pod, args=(rt, pod), daemon=True,
                                  name=f"pod-{rt.name}").start()
+
+    def _claim_gpus(self, want: int) -> Optional[List[int]]:
+        """Pick `want` free GPUs by topology and take their host-wide locks; a GPU another
+        launcher on this host holds is skipped. All or nothing."""
+        candidates = list(self._free_gpus)
+        while True:
+            gpus = self.topology.pick(want, candidates)
+            if gpus is None:
+                return None
+            got = []
+            for g in gpus:
+                if self._gpu_locks.acquire(g):
+                    got.append(g)
+                else:
+                    candidates.remove(g)
+            if len(got) == len(gpus):
+                return gpus
+            for g in got:
+                self._gpu_locks.release(g)
 
     def _fail_unschedulable(self, pod, message: str) -> None:
         st = pod.setdefault("status", {})
@@ -255,7 +313,8 @@ class LocalKubelet:
         labels = pod["metadata"].get("labels") or {}
         env.update({
             netmap.ENV_NAMESPACE: rt.ns, "TFOP_POD_NAME": rt.name,
-            "TFOP_POD_IP": netmap.pod_ip(rt.ns, rt.name),
+            "TFOP_POD_IP": netmap.pod_ip(rt.ns, rt.name, self.opt.cluster_id),
+            netmap.ENV_CLUSTER_ID: self.opt.cluster_id,
             "TFOP_JOB_NAME": labels.get(c.LABEL_JOB_NAME, ""),
             "TFOP_REPLICA_TYPE": labels.get(c.LABEL_REPLICA_TYPE, ""),
             "TFOP_REPLICA_INDEX": labels.get(c.LABEL_REPLICA_INDEX, ""),
@@ -319,7 +378,8 @@ class LocalKubelet:
             return
         st = pod.setdefault("status", {})
         st.update({"phase": phase, "containerStatuses": statuses,
-                   "podIP": netmap.pod_ip(rt.ns, rt.name), "hostIP": "127.0.0.1"})
+                   "podIP": netmap.pod_ip(rt.ns, rt.name, self.opt.cluster_id),
+                   "hostIP": "127.0.0.1"})
         st.setdefault("startTime", c.now_rfc3339())
         if reason:
             st["reason"] = reason
@@ -394,6 +454,7 @@ class LocalKubelet:
     def _release(self, rt: _PodRuntime) -> None:
         with self._lock:
             for g in rt.gpus:
+                self._gpu_locks.release(g)
                 if g not in self._free_gpus:
                     self._free_gpus.append(g)
             rt.gpus = []

@@ -4,9 +4,11 @@ In the reference every replica gets a headless Service whose DNS name
 ``<job>-<type>-<index>[.<ns>.svc[.<domain>]]`` resolves to the pod
 (pkg/controller.v1/tensorflow/tensorflow.go:153-166). On one box there is no DNS, but the
 whole 127.0.0.0/8 block is loopback on Linux, so every pod gets its own loopback IP derived
-from (namespace, name). All replicas can therefore keep the SAME well-known port (2222,
-23456, ...) without colliding, and any process can compute a peer's address from the name
-alone — no lookup service, nothing to race with pod start-up order.
+from (cluster id, namespace, name). All replicas can therefore keep the SAME well-known port
+(2222, 23456, ...) without colliding, and any process can compute a peer's address from the name
+alone — no lookup service, nothing to race with pod start-up order. The cluster id (one per
+LocalCluster, exported to replicas as ``TFOP_CLUSTER_ID``) keeps two clusters on one host - two
+operators, or parallel test sessions creating same-named jobs - on different addresses.
 """
 from __future__ import annotations
 
@@ -15,10 +17,14 @@ import os
 from typing import Tuple
 
 ENV_NAMESPACE = "TFOP_POD_NAMESPACE"
+ENV_CLUSTER_ID = "TFOP_CLUSTER_ID"
 
 
-def pod_ip(namespace: str, name: str) -> str:
-    h = hashlib.sha1(f"{namespace}/{name}".encode()).digest()
+def pod_ip(namespace: str, name: str, cluster_id: str | None = None) -> str:
+    if cluster_id is None:
+        cluster_id = os.environ.get(ENV_CLUSTER_ID, "")
+    key = f"{cluster_id}|{namespace}/{name}" if cluster_id else f"{namespace}/{name}"
+    h = hashlib.sha1(key.encode()).digest()
     a, b, c_ = h[0], h[1], h[2]
     if a == 0 and b == 0:
         b = 1                     # stay out of 127.0.0.x

@@ -56,4 +56,9 @@ def stem_conv_s2d(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     """conv2d(x, w) for the space-to-depth stem: x logical [N,16,H,W] channels-last, w [64,16,4,4]."""
     if _eligible(x, w):
         return _StemConv.apply(x, w)
+    if x.is_cuda:
+        raise ValueError(
+            f"stem_conv_s2d: the tcgen05 stem kernel takes bf16 channels-last [N,16,OH+3,OW+3] with "
+            f"OH % 8 == 0 and OW % 16 == 0 (image sides that are multiples of 32), got "
+            f"{tuple(x.shape)} {x.dtype}; feed the model the plain [N,3,H,W] input form instead")
     return F.conv2d(x, w)

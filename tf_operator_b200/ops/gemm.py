@@ -146,8 +146,12 @@ class _LinearFn(torch.autograd.Function):
 
 
 def linear(x, w, b=None, act: str = "none"):
-    """act(x @ w.T + b) — tcgen05 kernel for CUDA bf16, torch for everything else."""
-    if x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16:
+    """act(x @ w.T + b): the tcgen05 kernel for CUDA bf16 tensors, plain torch on the CPU. CUDA
+    tensors of another dtype raise - a layer built from this module never drops to a library
+    GEMM behind the caller's back (cast the model to bf16, or build it from nn.Linear)."""
+    if x.is_cuda:
+        if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+            raise TypeError(f"tcgen05 linear needs bf16 CUDA tensors, got {x.dtype} / {w.dtype}")
         return _LinearFn.apply(x, w, b, act)
     y = F.linear(x, w, b)
     if act == "gelu":

@@ -283,7 +283,10 @@ class DataParallelEngine(FlatDataParallel):
         # static device inputs / outputs (graph-friendly) + double-buffered staging
         shp = (batch_size, image_size, image_size, channels)
         self.x_u8 = torch.zeros(shp, dtype=torch.uint8, device=self.device)
-        self.stem_s2d = stem_s2d and channels == 3 and image_size % 2 == 0
+        # the tcgen05 stem kernel tiles the 2x-downsampled image in 8 x 16 pixel boxes: the
+        # space-to-depth input form is used for image sides that are multiples of 32, decided
+        # here once (other sizes get the plain input form and the stock 7x7 stem)
+        self.stem_s2d = stem_s2d and channels == 3 and image_size % 32 == 0
         xshp = (batch_size, image_size // 2 + 3, image_size // 2 + 3, 16) if self.stem_s2d else shp
         self.x_bf16 = torch.zeros(xshp, dtype=torch.bfloat16, device=self.device)
         self.labels = torch.zeros(batch_size, dtype=torch.int64, device=self.device)

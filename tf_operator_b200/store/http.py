@@ -203,7 +203,8 @@ class ApiServer:
             def _proxy(self, ns, svc_port, path, query):
                 from ..launcher import netmap
                 svc, _, port = svc_port.partition(":")
-                url = f"http://{netmap.pod_ip(ns, svc)}:{port}/{path}" + (f"?{query}" if query else "")
+                ip = netmap.pod_ip(ns, svc, getattr(outer.kubelet.opt, "cluster_id", None))
+                url = f"http://{ip}:{port}/{path}" + (f"?{query}" if query else "")
                 try:
                     with urllib.request.urlopen(url, timeout=10) as r:
                         self._send(r.status, r.read(), r.headers.get("Content-Type", "text/plain"))
