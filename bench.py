@@ -36,6 +36,57 @@ def _reference_arm():
     return 0
 
 
+def _through_the_product(args, world):
+    """The same job through the product's public API: a PyTorchJob submitted with
+    PyTorchJobClient to a LocalCluster (operator + launcher + rendezvous broker), one replica
+    process per GPU. Returns the launch latencies on real GPU replicas (p50 of --launch-trials)
+    and the throughput the launched ResNet-50 job reports (device-timed, max over ranks)."""
+    import tempfile
+    import yaml
+    from tf_operator_b200.cluster import LocalCluster
+    from tf_operator_b200.launcher.kubelet import KubeletOptions
+    from tf_operator_b200.sdk import PyTorchJobClient
+    from tf_operator_b200.testing import launch_probe
+    repo = os.path.dirname(os.path.abspath(__file__))
+    out = {}
+    cl = LocalCluster(kubelet_options=KubeletOptions(cwd=repo))
+    try:
+        if args.launch_trials > 0:
+            out["launch"] = launch_probe.measure(cl, world, args.launch_trials)
+        if not args.no_via_launcher:
+            job = yaml.safe_load(open(os.path.join(repo, "examples", "resnet50_ddp", "pytorchjob.yaml")))
+            res = os.path.join(tempfile.mkdtemp(prefix="tfop-bench-"), "result.json")
+            cmd = ["python", "examples/resnet50_ddp/train.py", f"--steps={args.steps}",
+                   f"--warmup={max(args.warmup, 3)}", f"--device-steps={args.steps}",
+                   f"--batch-size={args.batch_size}", f"--image-size={args.image_size}",
+                   f"--depth={args.depth}", f"--result-file={res}"]
+            specs = job["spec"]["pytorchReplicaSpecs"]
+            for rt in list(specs):
+                specs[rt]["template"]["spec"]["containers"][0]["command"] = cmd
+                specs[rt]["restartPolicy"] = "Never"
+            if world > 1:
+                specs["Worker"]["replicas"] = world - 1
+            else:
+                specs.pop("Worker", None)
+            cli = PyTorchJobClient(cluster=cl)
+            t0 = time.time()
+            cli.create(job)
+            name = job["metadata"]["name"]
+            cli.wait_for_job(name, polling_interval=0.2, timeout_seconds=600)
+            if not cli.is_job_succeeded(name):
+                raise RuntimeError(f"launched job failed: {cli.get_logs(name, master=True)}")
+            r = json.load(open(res))
+            out["via_launcher"] = {"value": r["device_img_per_s"], "unit": "img/s",
+                                   "ms_per_step": r["device_ms_per_step"],
+                                   "e2e_value": r["img_per_s"], "e2e_ms_per_step": r["ms_per_step"],
+                                   "allreduce": r["allreduce"], "job_wall_s": round(time.time() - t0, 1),
+                                   "api": "PyTorchJobClient.create -> LocalCluster -> "
+                                          "examples/resnet50_ddp/train.py replicas"}
+    finally:
+        cl.stop()
+    return out
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons during the timed region."""
 
@@ -108,6 +159,11 @@ def main():
                     help="use the P2P two-shot all-reduce even when NVLS multicast is available")
     ap.add_argument("--comm-blocks", type=int, default=32)
     ap.add_argument("--bucket-mb", type=int, default=16)
+    ap.add_argument("--launch-trials", type=int, default=10,
+                    help="PyTorchJobs of N real GPU replicas launched for the launch-to-Running / "
+                         "launch-to-first-step p50 (0 = skip)")
+    ap.add_argument("--no-via-launcher", action="store_true",
+                    help="skip re-running the config as a PyTorchJob through the operator + launcher")
     ap.add_argument("--stock-mode", default="autocast", choices=["autocast", "purebf16"],
                     help="--impl stock: fp32 weights under torch.autocast(bf16) (the usual recipe) "
                          "or a model cast to bf16")
@@ -168,11 +224,23 @@ def main():
         model = ResNet(args.depth, fused=not args.no_fused_bn)
         comm = None
         use_nvls = False
+        rdv_server = None
         if world > 1:
+            # The peer handles (CUDA IPC blobs, the NVLS multicast descriptor) travel through the
+            # launcher's own rendezvous store and descriptor broker - the code a PyTorchJob
+            # replica runs - hosted here by rank 0; torch.distributed only carries its address.
+            from tf_operator_b200.launcher.rendezvous import RendezvousServer
+            from tf_operator_b200.runtime.env import rendezvous_comm
+            where = [None]
+            if rank == 0:
+                rdv_server = RendezvousServer().start()
+                where = [(rdv_server.addr, rdv_server.uds_path)]
+            dist.broadcast_object_list(where, src=0)
             nparam = sum((p.numel() + 7) // 8 * 8 for p in model.parameters())
-            comm = SymmetricComm.from_torch_distributed(nparam * 2 + (8 << 20))
-            if not args.no_nvls:
-                use_nvls = comm.enable_nvls(nparam * 2 + (1 << 20))
+            comm = rendezvous_comm(where[0][0], where[0][1], f"bench/resnet/{os.getppid()}/comm0",
+                                   rank, world, nparam * 2 + (8 << 20),
+                                   nvls_bytes=0 if args.no_nvls else nparam * 2 + (1 << 20))
+            use_nvls = comm.nvls_bytes > 0
         eng = DataParallelEngine(model, comm=comm, batch_size=B, image_size=S, lr=0.1,
                                  momentum=0.9, weight_decay=1e-4, graph=not args.no_graph,
                                  overlap=not args.no_overlap, comm_blocks=args.comm_blocks,
@@ -275,6 +343,15 @@ def main():
     e2e_ms = max_over_ranks(max(f0.elapsed_time(f1), wall_ms))
     barrier()
 
+    # ---------------- the same job through the product (operator + launcher), rank 0 drives ----
+    product = {}
+    if args.impl == "native" and rank == 0 and (args.launch_trials > 0 or not args.no_via_launcher):
+        try:
+            product = _through_the_product(args, world)
+        except Exception as e:  # noqa: BLE001 - the headline numbers above stand on their own
+            product = {"error": f"{type(e).__name__}: {e}"[:500]}
+    barrier()
+
     if rank == 0:
         gb = B * world
         ms_step = ms_total / args.steps
@@ -304,8 +381,18 @@ def main():
                     "last_loss": round(last_loss, 4)},
             "gpu_launches": launches_per_step * args.steps,
         }
+        if product:
+            out.update({k: v for k, v in product.items()})
+            if "launch" in product:
+                out["launch_to_running_ms"] = product["launch"]["launch_to_running_ms"]
+                out["launch_to_first_step_ms"] = product["launch"]["launch_to_first_step_ms"]
         real_stdout.write(json.dumps(out) + "\n")
         real_stdout.flush()
+    if args.impl == "native":
+        if comm is not None:
+            comm.close()                 # exit barrier at the rendezvous store, then free
+        if rdv_server is not None:
+            rdv_server.stop()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -49,6 +49,8 @@ def main():
     ap.add_argument("--checkpoint-every", type=int, default=0)
     ap.add_argument("--comm-timeout-ms", type=int, default=0)
     ap.add_argument("--result-file", default="", help="rank 0 writes its final JSON line here too")
+    ap.add_argument("--device-steps", type=int, default=0,
+                    help="also time this many steps on the resident batch (no host traffic)")
     args = ap.parse_args()
 
     t_start = time.time()
@@ -87,6 +89,15 @@ def main():
             print(f"fault injection: rank {ctx.rank} kills itself at step {step}", flush=True)
             os.kill(os.getpid(), signal.SIGKILL)
 
+    def max_over_ranks(tag, value):
+        """device-timed numbers are the slowest rank's (values meet at the rendezvous store)"""
+        if comm is None or getattr(comm, "_rdv", None) is None:
+            return value
+        cli, prefix = comm._rdv
+        vals = cli.all_gather(f"{prefix}/max/{tag}", ctx.rank, ctx.world_size, repr(value).encode())
+        return max(float(v) for v in vals)
+
+    dev_ms = None
     try:
         first = True
         for _ in range(args.warmup):
@@ -98,6 +109,19 @@ def main():
                       flush=True)
             first = False
         torch.cuda.synchronize()
+        if args.device_steps:
+            d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if comm is not None:
+                comm._exit_barrier()
+            d0.record(eng.main_stream)
+            for _ in range(args.device_steps):
+                eng.run_device_step()
+            d1.record(eng.main_stream)
+            torch.cuda.synchronize()
+            dev_ms = max_over_ranks("dev", d0.elapsed_time(d1) / args.device_steps)
+            if comm is not None:
+                comm.raise_if_failed()
+                comm._exit_barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(eng.main_stream)
         pending, loss = None, float("nan")
@@ -122,10 +146,15 @@ def main():
     except CommError as e:
         print(f"rank {ctx.rank}: {e}; exiting {e.exit_code} (retryable)", flush=True)
         os._exit(e.exit_code)           # peers are gone: no exit barrier, no destructor
-    ms = e0.elapsed_time(e1) / max(1, args.steps - start_step)
+    ms = max_over_ranks("e2e", e0.elapsed_time(e1) / max(1, args.steps - start_step))
     if ctx.rank == 0:
         line = json.dumps({"img_per_s": round(B * ctx.world_size / (ms / 1e3), 1),
                            "ms_per_step": round(ms, 3), "world": ctx.world_size,
+                           "device_ms_per_step": round(dev_ms, 3) if dev_ms else None,
+                           "device_img_per_s": round(B * ctx.world_size / (dev_ms / 1e3), 1) if dev_ms else None,
+                           "kernel_launches_per_step": eng.kernel_launches_per_step,
+                           "h2d_bytes_per_step": eng.h2d_bytes_per_step(),
+                           "d2h_bytes_per_step": eng.d2h_bytes_per_step(),
                            "allreduce": "nvls" if use_nvls else ("p2p" if comm else None),
                            "generation": getattr(comm, "generation", 0),
                            "resumed_from": start_step, "final_loss": round(loss, 4)})

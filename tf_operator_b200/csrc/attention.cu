@@ -1,0 +1,655 @@
+// K13: multi-head self-attention (head dimension 64, no mask) on the tcgen05 tensor cores -
+// forward and backward, reading the PACKED projection output qkv[B*S, 3*H] exactly as the QKV
+// GEMM wrote it and writing the context as [B*S, H], so no transposed / unbound copy of Q, K or V
+// (nor their gradients) ever exists.
+//
+// Forward: one CTA per (128 queries, head, batch), two CTAs per SM so one CTA's softmax overlaps
+// the other's MMAs. Two passes over the keys (128 at a time, TMA ring):
+//   pass 1  S = Q K^T (tcgen05.mma, fp32 in TMEM) -> exact row maxima
+//   pass 2  S again -> P = exp2((S - max) * scale * log2 e) -> bf16 into a swizzled K-major
+//           shared-memory tile -> O += P V (V read as stored, MN-major) accumulated in TMEM
+//   end     O / rowsum -> bf16 -> TMA store; log-sum-exp (base 2) kept for the backward.
+// The second QK^T costs a third more tensor work (the kernel is bound by the exponentials, not
+// by the MMAs) and buys an O accumulator that never has to be rescaled.
+//
+// Reference parity: the attention of the BERT-large TFJob of BASELINE.json config 3 (the worker
+// matmuls of examples/v1/dist-mnist/dist_mnist.py:188-192 in the reference stack); replaces the
+// cuDNN scaled_dot_product_attention call.
+#include "common.cuh"
+#include "gemm_common.cuh"
+
+namespace {
+
+using namespace tfop_gemm;
+
+constexpr int kD = 64;          // head dimension
+constexpr int kBQ = 128;        // queries per CTA
+constexpr int kBK = 128;        // keys per block
+constexpr int kTile = 128 * 64 * 2;   // one [128 x 64] bf16 tile = 16 KB
+constexpr int kRing = 4;        // K / V ring slots
+constexpr int kFwdThreads = 256;
+constexpr int kFwdSmem = kTile /*Q*/ + kRing * kTile + 2 * kTile /*P*/ + 256 + 1024;
+constexpr int kFwdTmemCols = 256;  // S: [0,128), O: [128,192)
+
+struct AttnMaps {
+    CUtensorMap qkv;   // [B*S, 3H] bf16, box {64, 128}
+    CUtensorMap out;   // [B*S, H] bf16, box {64, 32} (store)
+};
+
+
+__global__ void __launch_bounds__(kFwdThreads, 2)
+attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, int S, int H,
+                int heads, float scale_log2e) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sq = smem;
+    uint8_t* sring = sq + kTile;
+    uint8_t* sp = sring + kRing * kTile;
+    uint64_t* bars = (uint64_t*)(sp + 2 * kTile);
+    uint64_t* q_full = bars;
+    uint64_t* r_full = bars + 1;            // [kRing]
+    uint64_t* r_empty = r_full + kRing;     // [kRing]
+    uint64_t* s_full = r_empty + kRing;     // MMA -> softmax: S ready
+    uint64_t* s_free = s_full + 1;          // softmax -> MMA: S read (pass 1) / P written (pass 2)
+    uint64_t* pv_done = s_free + 1;         // MMA -> softmax: P V finished reading P
+    uint32_t* tmem_slot = (uint32_t*)(pv_done + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qb = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
+    const int row0 = b * S + qb * kBQ;      // first query row of this CTA in [B*S, ...]
+    const int nkb = S / kBK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.qkv) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.out) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(q_full, 1);
+        for (int i = 0; i < kRing; ++i) {
+            mbar_init(&r_full[i], 1);
+            mbar_init(&r_empty[i], 1);
+        }
+        mbar_init(s_full, 1);
+        mbar_init(s_free, 4);
+        mbar_init(pv_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         smem_u32(tmem_slot)),
+                     "r"((uint32_t)kFwdTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 128u;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            mbar_expect_tx(q_full, kTile);
+            tma_load_2d(&maps.qkv, q_full, sq, head * kD, row0);
+            const int n_loads = 3 * nkb;   // pass 1: K_j; pass 2: K_j, V_j interleaved
+            for (int li = 0; li < n_loads; ++li) {
+                const int slot = li % kRing;
+                const uint32_t ph = (uint32_t)(li / kRing) & 1u;
+                int j, which;              // which: 1 = K, 2 = V (column block of qkv)
+                if (li < nkb) {
+                    j = li;
+                    which = 1;
+                } else {
+                    j = (li - nkb) >> 1;
+                    which = 1 + ((li - nkb) & 1);
+                }
+                mbar_wait(&r_empty[slot], ph ^ 1u);
+                mbar_expect_tx(&r_full[slot], kTile);
+                tma_load_2d(&maps.qkv, &r_full[slot], sring + slot * kTile, which * H + head * kD,
+                            b * S + j * kBK);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (elect_one()) {
+            const uint32_t idesc_s = make_idesc(kBQ, kBK);                   // S = Q K^T
+            const uint32_t idesc_o = make_idesc_major(kBQ, kD, 0, 1);        // O += P V (V MN-major)
+            const uint32_t q_addr = smem_u32(sq), p_addr = smem_u32(sp);
+            mbar_wait(q_full, 0);
+            tcgen05_fence_after();
+            int li = 0;
+            uint32_t sf = 0;              // s_free completions consumed so far
+            bool owe = false;             // a previous S has not been waited free yet
+            auto issue_s = [&](int slot) {
+                const uint32_t k_addr = smem_u32(sring + slot * kTile);
+#pragma unroll
+                for (int k = 0; k < kD / UMMA_K; ++k)
+                    umma_bf16(tmem_s, make_smem_desc(q_addr + k * 32), make_smem_desc(k_addr + k * 32),
+                              idesc_s, k != 0 ? 1u : 0u);
+                umma_commit(&r_empty[slot]);
+                umma_commit(s_full);
+            };
+            for (int pass = 0; pass < 2; ++pass)
+                for (int j = 0; j < nkb; ++j) {
+                    int slot = li % kRing;
+                    mbar_wait(&r_full[slot], (uint32_t)(li / kRing) & 1u);
+                    if (owe) {
+                        mbar_wait(s_free, sf & 1u);
+                        ++sf;
+                    }
+                    tcgen05_fence_after();
+                    issue_s(slot);
+                    owe = true;
+                    ++li;
+                    if (pass == 1) {
+                        slot = li % kRing;
+                        mbar_wait(&r_full[slot], (uint32_t)(li / kRing) & 1u);   // V_j
+                        mbar_wait(s_free, sf & 1u);                              // P_j written
+                        ++sf;
+                        owe = false;
+                        tcgen05_fence_after();
+                        const uint32_t v_addr = smem_u32(sring + slot * kTile);
+#pragma unroll
+                        for (int k = 0; k < kBK / UMMA_K; ++k) {
+                            // P: two K-major boxes of 64 keys; V: 128 key rows of 128 bytes
+                            const uint32_t pa = p_addr + (k >> 2) * kTile + (k & 3) * 32;
+                            umma_bf16(tmem_o, make_smem_desc(pa), make_smem_desc_mn(v_addr + k * 2048),
+                                      idesc_o, (j | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit(&r_empty[slot]);
+                        umma_commit(pv_done);
+                        ++li;
+                    }
+                }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===================== softmax: one thread per query row =====================
+        const int ew = warp - kEpiWarp0;
+        const int row = ew * 32 + lane;
+        const uint32_t t_s = tmem_s + ((uint32_t)(ew * 32) << 16);
+        const uint32_t t_o = tmem_o + ((uint32_t)(ew * 32) << 16);
+        uint32_t n_s = 0;                 // s_full completions consumed
+        float m = -INFINITY;
+        for (int j = 0; j < nkb; ++j) {   // pass 1: exact row maximum
+            mbar_wait(s_full, n_s & 1u);
+            ++n_s;
+            tcgen05_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < kBK; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(t_s + (uint32_t)c, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) m = fmaxf(m, __uint_as_float(r[i]));
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_free);
+        }
+        const float mc = m * scale_log2e;
+        float l = 0.f;
+        const uint32_t sw = (uint32_t)(row & 7);
+        uint8_t* prow = sp + (uint32_t)row * 128u;
+        for (int j = 0; j < nkb; ++j) {   // pass 2: probabilities
+            mbar_wait(s_full, n_s & 1u);
+            ++n_s;
+            tcgen05_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < kBK; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(t_s + (uint32_t)c, r);
+                tmem_ld_wait();
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float p0 = exp2f(fmaf(__uint_as_float(r[2 * i]), scale_log2e, -mc));
+                    const float p1 = exp2f(fmaf(__uint_as_float(r[2 * i + 1]), scale_log2e, -mc));
+                    const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+                    // the row sum is that of the ROUNDED probabilities the tensor core will use
+                    const float2 back = __bfloat1622float2(h2);
+                    l += back.x + back.y;
+                    pk[i] = *reinterpret_cast<const uint32_t*>(&h2);
+                }
+                if (c == 0 && j > 0) mbar_wait(pv_done, (uint32_t)(j - 1) & 1u);   // P buffer free
+                uint8_t* box = prow + (c >> 6) * kTile;      // keys 0-63 | 64-127
+                const uint32_t ch0 = (uint32_t)(c & 63) >> 3;  // first 16-byte chunk: 0 or 4
+#pragma unroll
+                for (uint32_t q = 0; q < 4; ++q)
+                    *reinterpret_cast<uint4*>(box + (((ch0 + q) ^ sw) << 4)) =
+                        make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+            }
+            tcgen05_fence_before();
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_free);
+        }
+        // ---- O / l -> bf16 -> swizzled box (the P tile is free now) -> TMA store; lse ----
+        mbar_wait(pv_done, (uint32_t)(nkb - 1) & 1u);
+        tcgen05_fence_after();
+        const float inv = 1.f / l;
+        uint8_t* obox = sp + ew * 4096;
+#pragma unroll 1
+        for (int c = 0; c < kD; c += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(t_o + (uint32_t)c, r);
+            tmem_ld_wait();
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]) * inv;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                bf16x8 v = f32_to_bf16x8(f + 8 * q);
+                *reinterpret_cast<uint4*>(obox + (uint32_t)lane * 128u +
+                                          ((((uint32_t)(c >> 3) + q) ^ (uint32_t)(lane & 7)) << 4)) =
+                    *reinterpret_cast<uint4*>(&v);
+            }
+        }
+        lse[((size_t)b * heads + head) * S + qb * kBQ + row] = mc + log2f(l);
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_2d(&maps.out, obox, head * kD, row0 + ew * 32);
+            bulk_commit();
+            bulk_wait_read<0>();
+        }
+        __syncwarp();
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                     "r"((uint32_t)kFwdTmemCols)
+                     : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward. One CTA per (128 keys, head, batch) - K_j and V_j stay in shared memory - looping over
+// the query blocks i. Everything is computed TRANSPOSED (keys on the 128 TMEM lanes, queries on
+// the columns), which makes every operand of the five products readable as it already sits in
+// shared memory:
+//   S^T  = K_j Q_i^T            A = K_j  (K-major)   B = Q_i  (K-major)
+//   dP^T = V_j dO_i^T           A = V_j  (K-major)   B = dO_i (K-major)
+//   threads: P^T = exp2(S^T c - lse_i), dS^T = P^T (dP^T - delta_i) / 8  -> bf16 tiles, K-major
+//   dV_j += P^T  dO_i           A = P^T  (K-major)   B = dO_i (MN-major, as stored)
+//   dK_j += dS^T Q_i            A = dS^T (K-major)   B = Q_i  (MN-major, as stored)
+//   dQ_i  = dS   K_j            A = dS^T read MN-major (it IS dS stored [key][query])
+//                                                    B = K_j  (MN-major, as stored)
+// dV_j / dK_j accumulate in TMEM over i and leave through TMA stores into the packed gradient
+// dqkv[B*S, 3H]; the dQ_i tiles of the S/128 CTAs of one (batch, head) meet in an fp32 buffer by
+// TMA reduce-add (attn_dq_convert_kernel rounds it into dqkv afterwards).
+constexpr int kBwdThreads = 256;
+constexpr int kBwdTmemCols = 512;   // S^T [0,128) dP^T [128,256) dV [256,320) dK [320,384) dQ [384,448)
+constexpr int kBwdSmem = 2 * kTile /*K V*/ + 4 * kTile /*Q dO x2*/ + 2 * kTile /*P^T*/ +
+                         2 * kTile /*dS^T*/ + 4 * 4096 /*staging*/ + 2 * 2 * 512 /*lse delta*/ +
+                         256 + 1024;
+static_assert(kBwdSmem <= 227 * 1024, "shared memory budget of one CTA");
+
+struct AttnBwdMaps {
+    CUtensorMap qkv;    // [B*S, 3H] bf16, box {64, 128}: Q, K, V loads
+    CUtensorMap dout;   // [B*S, H] bf16, box {64, 128}: dO loads
+    CUtensorMap dqkv;   // [B*S, 3H] bf16, box {64, 32}: dK, dV stores
+    CUtensorMap dq32;   // [B*S, H] fp32, box {32, 32}: dQ reduce-add
+};
+
+// MN-major operand whose 64-element halves along MN are `lbo` bytes apart (tiles of 128 k-rows)
+__device__ __forceinline__ uint64_t make_smem_desc_mn_lbo(uint32_t saddr, uint32_t lbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(lbo >> 4) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restrict__ lse,
+                const float* __restrict__ delta, int S, int H, int heads, float scale_log2e,
+                float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sk = smem;
+    uint8_t* sv = sk + kTile;
+    uint8_t* sqd = sv + kTile;              // 2 stages x (Q_i, dO_i)
+    uint8_t* spt = sqd + 4 * kTile;         // P^T   [128 keys][128 queries] as two 64-query boxes
+    uint8_t* sdst = spt + 2 * kTile;        // dS^T  same layout
+    uint8_t* sstage = sdst + 2 * kTile;     // 4 x 4 KB store staging
+    float* svec = (float*)(sstage + 4 * 4096);   // [2 stages][lse | delta][128]
+    uint64_t* bars = (uint64_t*)((uint8_t*)svec + 2 * 2 * 512);
+    uint64_t* kv_full = bars;
+    uint64_t* qd_full = bars + 1;           // [2]
+    uint64_t* qd_empty = qd_full + 2;       // [2]
+    uint64_t* s_full = qd_empty + 2;        // MMA -> threads: S^T and dP^T of block i ready
+    uint64_t* p_ready = s_full + 1;         // threads -> MMA: P^T / dS^T written, S^T / dP^T / dQ read
+    uint64_t* mma2_done = p_ready + 1;      // MMA -> threads: dV, dK, dQ_i products of block i done
+    uint32_t* tmem_slot = (uint32_t*)(mma2_done + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int jb = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
+    const int krow0 = b * S + jb * kBK;
+    const int nqb = S / kBQ;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.qkv) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.dout) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.dqkv) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.dq32) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(kv_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&qd_full[i], 1);
+            mbar_init(&qd_empty[i], 1);
+        }
+        mbar_init(s_full, 1);
+        mbar_init(p_ready, 4);
+        mbar_init(mma2_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         smem_u32(tmem_slot)),
+                     "r"((uint32_t)kBwdTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t t_st = tmem_base, t_dpt = tmem_base + 128u, t_dv = tmem_base + 256u,
+                   t_dk = tmem_base + 320u, t_dq = tmem_base + 384u;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            mbar_expect_tx(kv_full, 2 * kTile);
+            tma_load_2d(&maps.qkv, kv_full, sk, H + head * kD, krow0);
+            tma_load_2d(&maps.qkv, kv_full, sv, 2 * H + head * kD, krow0);
+            for (int i = 0; i < nqb; ++i) {
+                const int st = i & 1;
+                mbar_wait(&qd_empty[st], ((uint32_t)(i >> 1) & 1u) ^ 1u);
+                mbar_expect_tx(&qd_full[st], 2 * kTile);
+                tma_load_2d(&maps.qkv, &qd_full[st], sqd + st * 2 * kTile, head * kD, b * S + i * kBQ);
+                tma_load_2d(&maps.dout, &qd_full[st], sqd + st * 2 * kTile + kTile, head * kD,
+                            b * S + i * kBQ);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (elect_one()) {
+            const uint32_t id_s = make_idesc(128, 128);                 // both K-major
+            const uint32_t id_acc = make_idesc_major(128, kD, 0, 1);    // A K-major, B MN-major
+            const uint32_t id_dq = make_idesc_major(128, kD, 1, 1);     // both MN-major
+            const uint32_t k_addr = smem_u32(sk), v_addr = smem_u32(sv);
+            const uint32_t pt_addr = smem_u32(spt), dst_addr = smem_u32(sdst);
+            mbar_wait(kv_full, 0);
+            for (int i = 0; i < nqb; ++i) {
+                const int st = i & 1;
+                mbar_wait(&qd_full[st], (uint32_t)(i >> 1) & 1u);
+                tcgen05_fence_after();
+                const uint32_t q_addr = smem_u32(sqd + st * 2 * kTile), do_addr = q_addr + kTile;
+#pragma unroll
+                for (int k = 0; k < kD / UMMA_K; ++k)
+                    umma_bf16(t_st, make_smem_desc(k_addr + k * 32), make_smem_desc(q_addr + k * 32),
+                              id_s, k != 0 ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < kD / UMMA_K; ++k)
+                    umma_bf16(t_dpt, make_smem_desc(v_addr + k * 32), make_smem_desc(do_addr + k * 32),
+                              id_s, k != 0 ? 1u : 0u);
+                umma_commit(s_full);
+                mbar_wait(p_ready, (uint32_t)i & 1u);
+                tcgen05_fence_after();
+#pragma unroll
+                for (int k = 0; k < 128 / UMMA_K; ++k) {
+                    // K-major A tiles: two 64-query boxes; MN-major B: 128 rows of 128 bytes
+                    const uint32_t aoff = (k >> 2) * kTile + (k & 3) * 32;
+                    umma_bf16(t_dv, make_smem_desc(pt_addr + aoff), make_smem_desc_mn(do_addr + k * 2048),
+                              id_acc, (i | k) != 0 ? 1u : 0u);
+                    umma_bf16(t_dk, make_smem_desc(dst_addr + aoff), make_smem_desc_mn(q_addr + k * 2048),
+                              id_acc, (i | k) != 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int k = 0; k < 128 / UMMA_K; ++k)
+                    umma_bf16(t_dq, make_smem_desc_mn_lbo(dst_addr + k * 2048, kTile),
+                              make_smem_desc_mn(k_addr + k * 2048), id_dq, k != 0 ? 1u : 0u);
+                umma_commit(&qd_empty[st]);
+                umma_commit(mma2_done);
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===================== one thread per key row =====================
+        const int ew = warp - kEpiWarp0;
+        const int row = ew * 32 + lane;
+        const uint32_t lane_sel = (uint32_t)(ew * 32) << 16;
+        const uint32_t sw = (uint32_t)(row & 7);
+        uint8_t* ptrow = spt + (uint32_t)row * 128u;
+        uint8_t* dstrow = sdst + (uint32_t)row * 128u;
+        uint8_t* stage = sstage + ew * 4096;
+        const size_t vec0 = ((size_t)b * heads + head) * S;
+        // fp32 [32 rows x 32 cols] of a TMEM accumulator -> swizzled staging box -> TMA
+        auto flush_f32 = [&](uint32_t taddr, int col, int grow) {
+#pragma unroll 1
+            for (int c = 0; c < kD; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + lane_sel + (uint32_t)c, r);
+                tmem_ld_wait();
+                if (lane == 0) bulk_wait_read<0>();
+                __syncwarp();
+#pragma unroll
+                for (uint32_t q = 0; q < 8; ++q)
+                    *reinterpret_cast<uint4*>(stage + (uint32_t)lane * 128u + ((q ^ (uint32_t)(lane & 7)) << 4)) =
+                        make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_reduce_add_2d(&maps.dq32, stage, col + c, grow);
+                    bulk_commit();
+                }
+            }
+        };
+        for (int i = 0; i < nqb; ++i) {
+            float* vec = svec + (i & 1) * 256;
+            vec[row] = lse[vec0 + i * kBQ + row];
+            vec[128 + row] = delta[vec0 + i * kBQ + row];
+            epi_bar_sync();
+            mbar_wait(s_full, (uint32_t)i & 1u);
+            tcgen05_fence_after();
+            // dQ of the previous query block (its MMAs precede this block's S^T in issue order)
+            if (i > 0) flush_f32(t_dq, head * kD, b * S + (i - 1) * kBQ + ew * 32);
+#pragma unroll 1
+            for (int c = 0; c < kBQ; c += 32) {
+                uint32_t rs[32], rd[32];
+                tmem_ld_32x32b_x32(t_st + lane_sel + (uint32_t)c, rs);
+                tmem_ld_32x32b_x32(t_dpt + lane_sel + (uint32_t)c, rd);
+                tmem_ld_wait();
+                uint32_t pk[16], dk[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const float2 l2 = *reinterpret_cast<const float2*>(vec + c + 2 * k);
+                    const float2 d2 = *reinterpret_cast<const float2*>(vec + 128 + c + 2 * k);
+                    const float p0 = exp2f(fmaf(__uint_as_float(rs[2 * k]), scale_log2e, -l2.x));
+                    const float p1 = exp2f(fmaf(__uint_as_float(rs[2 * k + 1]), scale_log2e, -l2.y));
+                    const float s0 = p0 * (__uint_as_float(rd[2 * k]) - d2.x) * scale;
+                    const float s1 = p1 * (__uint_as_float(rd[2 * k + 1]) - d2.y) * scale;
+                    const __nv_bfloat162 ph = __floats2bfloat162_rn(p0, p1);
+                    const __nv_bfloat162 dh = __floats2bfloat162_rn(s0, s1);
+                    pk[k] = *reinterpret_cast<const uint32_t*>(&ph);
+                    dk[k] = *reinterpret_cast<const uint32_t*>(&dh);
+                }
+                const uint32_t boff = (uint32_t)(c >> 6) * kTile;
+                const uint32_t ch0 = (uint32_t)(c & 63) >> 3;
+#pragma unroll
+                for (uint32_t q = 0; q < 4; ++q) {
+                    const uint32_t off = boff + (((ch0 + q) ^ sw) << 4);
+                    *reinterpret_cast<uint4*>(ptrow + off) =
+                        make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                    *reinterpret_cast<uint4*>(dstrow + off) =
+                        make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+                }
+            }
+            tcgen05_fence_before();
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_ready);
+        }
+        mbar_wait(mma2_done, (uint32_t)(nqb - 1) & 1u);
+        tcgen05_fence_after();
+        flush_f32(t_dq, head * kD, b * S + (nqb - 1) * kBQ + ew * 32);
+        // dV_j, dK_j: fp32 TMEM -> bf16 -> swizzled box -> TMA store into the packed gradient
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {
+            const uint32_t taddr = (which == 0 ? t_dv : t_dk) + lane_sel;
+            if (lane == 0) bulk_wait_read<0>();
+            __syncwarp();
+#pragma unroll 1
+            for (int c = 0; c < kD; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + (uint32_t)c, r);
+                tmem_ld_wait();
+                float f[32];
+#pragma unroll
+                for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(r[k]);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    bf16x8 v = f32_to_bf16x8(f + 8 * q);
+                    *reinterpret_cast<uint4*>(stage + (uint32_t)lane * 128u +
+                                              ((((uint32_t)(c >> 3) + q) ^ (uint32_t)(lane & 7)) << 4)) =
+                        *reinterpret_cast<uint4*>(&v);
+                }
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&maps.dqkv, stage, (which == 0 ? 2 * H : H) + head * kD, krow0 + ew * 32);
+                bulk_commit();
+            }
+        }
+        if (lane == 0) bulk_wait_read<0>();
+        __syncwarp();
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                     "r"((uint32_t)kBwdTmemCols)
+                     : "memory");
+    }
+}
+
+// delta[b, head, s] = sum_d dO[row, head*64 + d] * O[row, head*64 + d]  (8 lanes per (row, head))
+__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ dout,
+                                  const __nv_bfloat16* __restrict__ out, float* __restrict__ delta,
+                                  int B, int S, int heads) {
+    const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long item = t >> 3;                       // (row, head)
+    const int part = (int)(t & 7);
+    const long n_items = (long)B * S * heads;
+    float acc = 0.f;
+    long row = 0;
+    int head = 0;
+    if (item < n_items) {
+        row = item / heads;
+        head = (int)(item - row * heads);
+        const size_t off = (size_t)row * heads * kD + head * kD + part * 8;
+        float a[8], o[8];
+        bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(dout + off), a);
+        bf16x8_to_f32(*reinterpret_cast<const bf16x8*>(out + off), o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc = fmaf(a[k], o[k], acc);
+    }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (item < n_items && part == 0) {
+        const long b = row / S, s = row - b * S;
+        delta[((size_t)b * heads + head) * S + s] = acc;
+    }
+}
+
+// dqkv[row, 0:H] = bf16(dq32[row, :])   (8 elements per thread)
+__global__ void attn_dq_convert_kernel(const float* __restrict__ dq32, __nv_bfloat16* __restrict__ dqkv,
+                                       long rows, int H) {
+    const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int per_row = H / 8;
+    if (t >= rows * per_row) return;
+    const long row = t / per_row;
+    const int c = (int)(t - row * per_row) * 8;
+    const float4 a = *reinterpret_cast<const float4*>(dq32 + row * H + c);
+    const float4 b = *reinterpret_cast<const float4*>(dq32 + row * H + c + 4);
+    const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    bf16x8 v = f32_to_bf16x8(f);
+    *reinterpret_cast<uint4*>(dqkv + row * 3 * H + c) = *reinterpret_cast<uint4*>(&v);
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 g_enc = nullptr;
+
+int get_enc() {
+    if (g_enc) return 0;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    TFOP_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    TFOP_REQUIRE(qres == cudaDriverEntryPointSuccess && fn != nullptr,
+                 "cuTensorMapEncodeTiled not available from the driver");
+    g_enc = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+    return 0;
+}
+
+// 2-D row-major [rows, cols] tensor, box {box_cols, box_rows}
+int map2d(CUtensorMap* map, const void* base, long rows, long cols, int box_cols, int box_rows,
+          CUtensorMapDataType dt, int elt, CUtensorMapSwizzle swz, const char* what) {
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * elt};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_enc(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char msg[128];
+        snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, (int)r);
+        tfop_set_error(__FILE__, __LINE__, msg);
+        return -1;
+    }
+    return 0;
+}
+
+int check_attn(const void* a, const void* b, int B, int S, int heads, int d) {
+    TFOP_REQUIRE(B > 0 && heads > 0, "attention: empty problem");
+    TFOP_REQUIRE(d == kD, "attention: head dimension must be 64");
+    TFOP_REQUIRE(S > 0 && S % 128 == 0, "attention: sequence length must be a multiple of 128");
+    TFOP_REQUIRE(((((uintptr_t)a) | ((uintptr_t)b)) & 15) == 0, "attention: tensors must be 16-byte aligned");
+    return 0;
+}
+
+}  // namespace
+
+// out[B*S, H] = softmax(Q K^T / sqrt(64)) V per (batch, head), H = heads * 64, for the packed
+// qkv[B*S, 3H] = [Q | K | V] (bf16, row-major). lse[B, heads, S] (fp32) receives the base-2
+// log-sum-exp of the scaled scores, which tfop_attn_bwd needs.
+TFOP_API int tfop_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int heads,
+                           int head_dim, cudaStream_t stream) {
+    if (check_attn(qkv, out, B, S, heads, head_dim) != 0) return -1;
+    if (get_enc() != 0) return -1;
+    const int H = heads * kD;
+    AttnMaps maps;
+    if (map2d(&maps.qkv, qkv, (long)B * S, 3L * H, 64, 128, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+              CU_TENSOR_MAP_SWIZZLE_128B, "qkv"))
+        return -1;
+    if (map2d(&maps.out, out, (long)B * S, H, 64, 32, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+              CU_TENSOR_MAP_SWIZZLE_128B, "out"))
+        return -1;
+    TFOP_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   kFwdSmem));
+    const float scale_log2e = 0.125f * 1.4426950408889634f;
+    attn_fwd_kernel<<<dim3(S / kBQ, heads, B), kFwdThreads, kFwdSmem, stream>>>(maps, lse, S, H,
+                                                                                 heads, scale_log2e);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}

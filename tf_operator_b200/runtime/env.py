@@ -155,22 +155,32 @@ class ReplicaContext:
         from .symm import SymmetricComm
         addr = self.raw.get("TFOP_RENDEZVOUS")
         if addr and self.world_size > 1:
-            from ..launcher.rendezvous import RendezvousClient
-            cli = RendezvousClient(addr, uds_path=self.raw.get("TFOP_RENDEZVOUS_UDS", ""))
-            # join the gang's current generation (a restarted replica opens a new one, its peers
-            # follow once their collectives have timed out and the operator has restarted them)
-            scope = self.rendezvous_scope(tag)
-            gen = cli.join(scope, self.rank, self.world_size)
-            prefix = f"{scope}/g{gen}"
-            comm = SymmetricComm.create(
-                self.rank, self.world_size, nbytes,
-                lambda b: cli.all_gather(prefix + "/ipc", self.rank, self.world_size, b))
-            cli.barrier(prefix + "/ready", self.world_size)
-            comm._rdv = (cli, prefix)
-            comm.generation = gen
-            world = self.world_size
-            comm._exit_barrier = lambda: cli.barrier(prefix + "/exit", world, timeout=60)
-            return comm
+            return rendezvous_comm(addr, self.raw.get("TFOP_RENDEZVOUS_UDS", ""),
+                                   self.rendezvous_scope(tag), self.rank, self.world_size, nbytes)
         if self.world_size > 1:
             return SymmetricComm.from_torch_distributed(nbytes)
         return SymmetricComm.create(0, 1, nbytes, lambda b: [b])
+
+
+def rendezvous_comm(addr: str, uds_path: str, scope: str, rank: int, world: int, nbytes: int,
+                    nvls_bytes: int = 0):
+    """Form a SymmetricComm through a launcher rendezvous store at ``addr`` (descriptor broker at
+    ``uds_path``): join the scope's current generation (a restarted replica opens a new one, its
+    peers follow once their collectives have timed out and the operator has restarted them),
+    exchange the CUDA IPC handles under ``<scope>/g<generation>/``, barrier. The communicator
+    keeps the client for the NVLS descriptor hand-off and for its exit barrier."""
+    from ..launcher.rendezvous import RendezvousClient
+    from .symm import SymmetricComm
+    cli = RendezvousClient(addr, uds_path=uds_path)
+    gen = cli.join(scope, rank, world)
+    prefix = f"{scope}/g{gen}"
+    comm = SymmetricComm.create(rank, world, nbytes,
+                                lambda b: cli.all_gather(prefix + "/ipc", rank, world, b))
+    cli.barrier(prefix + "/ready", world)
+    comm._rdv = (cli, prefix)
+    comm.generation = gen
+    comm._exit_barrier = lambda: cli.barrier(prefix + "/exit", world, timeout=60)
+    comm.nvls_bytes = 0
+    if nvls_bytes:
+        comm.enable_nvls(nvls_bytes)
+    return comm
