@@ -43,6 +43,17 @@ size_t tfop_comm_buffer_bytes(tfop_comm* c);
 int tfop_comm_rank(tfop_comm* c);
 int tfop_comm_world(tfop_comm* c);
 int tfop_comm_check_error(tfop_comm* c, int* flag);
+/* Spin limit of every cross-rank flag barrier, in ms of a 2 GHz SM clock (default 120,000). When
+ * it expires the kernel ABANDONS the collective (reduces and stores nothing) and sets the
+ * communicator's error word; the replica is expected to exit with a retryable code so the
+ * operator re-creates it (restartPolicy ExitCode, pkg/controller.v1/tensorflow/pod.go:140-159). */
+int tfop_comm_set_timeout_ms(long long ms);
+/* Device address of the error word (uint32, 0 = healthy) for asynchronous polling. */
+void* tfop_comm_error_ptr(tfop_comm* c);
+/* tfop_comm_destroy refuses (returns an error, frees nothing) while peers may still read or
+ * write this rank's buffers: run a cross-rank exit barrier after the last collective, call
+ * tfop_comm_quiesce, then destroy. Single-rank and emulated communicators need no quiesce. */
+int tfop_comm_quiesce(tfop_comm* c);
 int tfop_comm_destroy(tfop_comm* c);
 
 /* ---- K1/K6/K8: fused P2P all-reduce (csrc/allreduce.cu) ------------------
@@ -289,6 +300,41 @@ int tfop_gemm_allreduce_emulated(tfop_comm** comms, int world, const void* const
                                  const void* const* Bs, int M, int N, int K, int lda, int ldb,
                                  int ldo, float scale, size_t ws_off, size_t out_off,
                                  cudaStream_t stream);
+
+/* ---- NHWC bf16 convolutions on tcgen05 implicit GEMMs (csrc/conv_tc.cu) --------------------
+ * The Conv2D layers of keras-API/multi_worker_strategy-with-keras.py:42-60 (cuDNN in the
+ * reference stack). x[N,H,W,Cin], w[Cout,k,k,Cin] (KRSC), y[N,OH,OW,Cout]; k in {1,3}, stride in
+ * {1,2}, padding k/2, channel counts multiples of 64. `stats` (may be NULL): [2,Cout] fp32 to
+ * which the per-channel sum and sum of squares of y are ADDED (BatchNorm statistics without a
+ * pass over y, see tfop_bn_finalize). tfop_conv_dgrad with accumulate != 0 ADDS the gradient into
+ * dx (the shortcut branch's gradient) by TMA reduce-add. tfop_conv_wgrad adds fp32 partial tiles
+ * into dw[Cout,k,k,Cin], which the caller zeroes. */
+int tfop_conv_fwd(const void* x, const void* w, void* y, float* stats, int N, int H, int W,
+                  int Cin, int Cout, int ksize, int stride, cudaStream_t stream);
+int tfop_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin,
+                    int Cout, int ksize, int stride, int accumulate, cudaStream_t stream);
+int tfop_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin,
+                    int Cout, int ksize, int stride, cudaStream_t stream);
+/* Test hook: -1 auto, 0 never pair CTAs (cta_group::2), 1 pair wherever the tile allows. */
+int tfop_conv_set_cluster_mode(int mode);
+/* BatchNorm statistics from sums[2][C] a convolution epilogue accumulated over M rows: same
+ * outputs as tfop_bn_fwd_stats; clears `sums` for the next step. */
+int tfop_bn_finalize(float* sums, size_t M, int C, const void* gamma, const void* beta,
+                     int param_dtype, float* running_mean, float* running_var, float momentum,
+                     float eps, float* scale_shift, float* save_mean, float* save_invstd,
+                     cudaStream_t stream);
+
+/* ---- multi-head self-attention, head dimension 64, no mask (csrc/attention.cu) --------------
+ * Worker-side math of the BERT-large TFJob (the reference's trainers compute in
+ * examples/v1/dist-mnist/dist_mnist.py:188-192). qkv[B*S, 3H] = [Q | K | V] packed as the
+ * projection GEMM writes it, H = heads * 64, S a multiple of 128; out[B*S, H];
+ * lse[B, heads, S] fp32 (base-2 log-sum-exp). tfop_attn_bwd writes dqkv[B*S, 3H] in the layout
+ * of qkv; delta[B, heads, S] and dq32[B*S, H] (fp32) are caller-provided scratch. */
+int tfop_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int heads, int head_dim,
+                  cudaStream_t stream);
+int tfop_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
+                  void* dqkv, float* delta, float* dq32, int B, int S, int heads, int head_dim,
+                  cudaStream_t stream);
 
 #ifdef __cplusplus
 }

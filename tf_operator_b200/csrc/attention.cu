@@ -26,7 +26,7 @@ constexpr int kD = 64;          // head dimension
 constexpr int kBQ = 128;        // queries per CTA
 constexpr int kBK = 128;        // keys per block
 constexpr int kTile = 128 * 64 * 2;   // one [128 x 64] bf16 tile = 16 KB
-constexpr int kRing = 4;        // K / V ring slots
+constexpr int kRing = 3;        // K / V ring slots (two CTAs of 100 KB fit one SM)
 constexpr int kFwdThreads = 256;
 constexpr int kFwdSmem = kTile /*Q*/ + kRing * kTile + 2 * kTile /*P*/ + 256 + 1024;
 constexpr int kFwdTmemCols = 256;  // S: [0,128), O: [128,192)
@@ -590,7 +590,18 @@ __global__ void attn_dq_convert_kernel(const float* __restrict__ dq32, __nv_bflo
 
 PFN_cuTensorMapEncodeTiled_v12000 g_enc = nullptr;
 
+// A driver-API call (cuTensorMapEncodeTiled) needs a current context on the calling thread. An
+// autograd worker thread whose first GPU work is one of these entry points may have none yet:
+// cudaSetDevice on the thread's current device binds the primary context (legal under capture).
+static int bind_context() {
+    int dev = 0;
+    TFOP_CUDA(cudaGetDevice(&dev));
+    TFOP_CUDA(cudaSetDevice(dev));
+    return 0;
+}
+
 int get_enc() {
+    if (bind_context() != 0) return -1;
     if (g_enc) return 0;
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
@@ -650,6 +661,52 @@ TFOP_API int tfop_attn_fwd(const void* qkv, void* out, float* lse, int B, int S,
     const float scale_log2e = 0.125f * 1.4426950408889634f;
     attn_fwd_kernel<<<dim3(S / kBQ, heads, B), kFwdThreads, kFwdSmem, stream>>>(maps, lse, S, H,
                                                                                  heads, scale_log2e);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Gradient of tfop_attn_fwd. dqkv[B*S, 3H] (bf16) receives [dQ | dK | dV] in the layout of qkv,
+// i.e. it IS the gradient of the packed projection output. `out` and `lse` are the forward's
+// results. Scratch (caller-provided, so the call allocates nothing): delta[B, heads, S] fp32 and
+// dq32[B*S, H] fp32; dq32 is zeroed here and holds the unrounded dQ afterwards.
+TFOP_API int tfop_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
+                           void* dqkv, float* delta, float* dq32, int B, int S, int heads,
+                           int head_dim, cudaStream_t stream) {
+    if (check_attn(qkv, dqkv, B, S, heads, head_dim) != 0) return -1;
+    TFOP_REQUIRE(((((uintptr_t)out) | ((uintptr_t)dout) | ((uintptr_t)dq32)) & 15) == 0,
+                 "attention: tensors must be 16-byte aligned");
+    if (get_enc() != 0) return -1;
+    const int H = heads * kD;
+    const long rows = (long)B * S;
+    AttnBwdMaps maps;
+    if (map2d(&maps.qkv, qkv, rows, 3L * H, 64, 128, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+              CU_TENSOR_MAP_SWIZZLE_128B, "qkv"))
+        return -1;
+    if (map2d(&maps.dout, dout, rows, H, 64, 128, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+              CU_TENSOR_MAP_SWIZZLE_128B, "dout"))
+        return -1;
+    if (map2d(&maps.dqkv, dqkv, rows, 3L * H, 64, 32, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+              CU_TENSOR_MAP_SWIZZLE_128B, "dqkv"))
+        return -1;
+    if (map2d(&maps.dq32, dq32, rows, H, 32, 32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+              CU_TENSOR_MAP_SWIZZLE_128B, "dq32"))
+        return -1;
+    TFOP_CUDA(cudaMemsetAsync(dq32, 0, (size_t)rows * H * 4, stream));
+    {
+        const long threads = rows * heads * 8;
+        attn_delta_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+            (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, delta, B, S, heads);
+    }
+    TFOP_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   kBwdSmem));
+    const float scale = 0.125f;
+    attn_bwd_kernel<<<dim3(S / kBK, heads, B), kBwdThreads, kBwdSmem, stream>>>(
+        maps, lse, delta, S, H, heads, scale * 1.4426950408889634f, scale);
+    {
+        const long threads = rows * (H / 8);
+        attn_dq_convert_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+            dq32, (__nv_bfloat16*)dqkv, rows, H);
+    }
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }

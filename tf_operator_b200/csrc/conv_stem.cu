@@ -451,6 +451,11 @@ TFOP_API int tfop_conv_stem_s2d_fwd(const void* x, const void* w, void* y, int n
                  "conv_stem: OH must be a multiple of 8 and OW a multiple of 16");
     TFOP_REQUIRE(((((uintptr_t)x) | ((uintptr_t)w) | ((uintptr_t)y)) & 15) == 0,
                  "conv_stem: tensors must be 16-byte aligned");
+    {   // bind the primary context on this thread (see gemm_tcgen05.cu: bind_context)
+        int dev_ = 0;
+        TFOP_CUDA(cudaGetDevice(&dev_));
+        TFOP_CUDA(cudaSetDevice(dev_));
+    }
     if (!g_enc) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -522,6 +527,11 @@ TFOP_API int tfop_conv_stem_s2d_wgrad(const void* x, const void* dy, float* dw, 
                  "conv_stem wgrad: OH must be a multiple of 4 and OW a multiple of 16");
     TFOP_REQUIRE(((((uintptr_t)x) | ((uintptr_t)dy) | ((uintptr_t)dw)) & 15) == 0,
                  "conv_stem: tensors must be 16-byte aligned");
+    {   // bind the primary context on this thread (see gemm_tcgen05.cu: bind_context)
+        int dev_ = 0;
+        TFOP_CUDA(cudaGetDevice(&dev_));
+        TFOP_CUDA(cudaSetDevice(dev_));
+    }
     if (!g_enc) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;

@@ -486,7 +486,18 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 
 PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 
+// A driver-API call (cuTensorMapEncodeTiled) needs a current context on the calling thread. An
+// autograd worker thread whose first GPU work is one of these entry points may have none yet:
+// cudaSetDevice on the thread's current device binds the primary context (legal under capture).
+static int bind_context() {
+    int dev = 0;
+    TFOP_CUDA(cudaGetDevice(&dev));
+    TFOP_CUDA(cudaSetDevice(dev));
+    return 0;
+}
+
 int get_encode() {
+    if (bind_context() != 0) return -1;
     if (g_encode) return 0;
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;

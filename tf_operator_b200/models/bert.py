@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops.attention import attention
 from ..ops.gemm import TcLinear, linear
 from ..ops.layernorm import add_bias_layernorm, bias_gelu
 from ..ops.xent import softmax_cross_entropy
@@ -77,12 +78,18 @@ class BertLayer(nn.Module):
 
     def forward(self, x, mask=None):
         b, s, h = x.shape
-        # unbind (not permute + index): its backward is one stack copy instead of three
-        # zero-filled [3, ...] tensors that are then added
-        q, k, v = self.qkv(x).view(b, s, 3, self.heads, h // self.heads).unbind(2)
-        a = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2),
-                                           attn_mask=mask)
-        a = a.transpose(1, 2).reshape(b, s, h)
+        if self.fused and mask is None and x.is_cuda and h // self.heads == 64 and s % 128 == 0:
+            # tcgen05 attention straight on the packed projection output: no unbind / transpose
+            # copies forward, no cat backward (ops/attention.py, csrc/attention.cu)
+            a = attention(self.qkv(x), self.heads)
+        else:
+            # library path: the stock twin, masks, other head sizes, CPU
+            # unbind (not permute + index): its backward is one stack copy instead of three
+            # zero-filled [3, ...] tensors that are then added
+            q, k, v = self.qkv(x).view(b, s, 3, self.heads, h // self.heads).unbind(2)
+            a = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2),
+                                               v.transpose(1, 2), attn_mask=mask)
+            a = a.transpose(1, 2).reshape(b, s, h)
         if not self.fused:
             x = self.ln1(x + self.proj(a))
             return self.ln2(x + self.fc2(self.fc1(x)))

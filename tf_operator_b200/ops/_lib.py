@@ -126,6 +126,8 @@ _SIGS = {
     "tfop_conv_dgrad": (c_int, [c_void_p] * 3 + [c_int] * 8 + [c_void_p]),
     "tfop_conv_wgrad": (c_int, [c_void_p] * 3 + [c_int] * 7 + [c_void_p]),
     "tfop_conv_set_cluster_mode": (c_int, [c_int]),
+    "tfop_attn_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "tfop_attn_bwd": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
     "tfop_transpose_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
