@@ -3,8 +3,11 @@
 // GEMM wrote it and writing the context as [B*S, H], so no transposed / unbound copy of Q, K or V
 // (nor their gradients) ever exists.
 //
-// Forward: one CTA per (128 queries, head, batch), two CTAs per SM so one CTA's softmax overlaps
-// the other's MMAs. Two passes over the keys (128 at a time, TMA ring):
+// Forward: persistent CTAs (one per SM) walk the (batch, head, 128-query) tiles. Two passes over
+// the keys of a tile (128 at a time, TMA ring), software-pipelined over THREE S accumulators in
+// TMEM and TWO P tiles in shared memory so the MMA thread runs ahead of the softmax warps (the
+// first version - one S, one P, everything a serial MMA -> softmax -> MMA round trip - left the
+// tensor pipe 18 % and the MUFU pipe 27 % busy: ncu, profiles/r2_ncu_attention.md):
 //   pass 1  S = Q K^T (tcgen05.mma, fp32 in TMEM) -> exact row maxima
 //   pass 2  S again -> P = exp2((S - max) * scale * log2 e) -> bf16 into a swizzled K-major
 //           shared-memory tile -> O += P V (V read as stored, MN-major) accumulated in TMEM
@@ -26,52 +29,71 @@ constexpr int kD = 64;          // head dimension
 constexpr int kBQ = 128;        // queries per CTA
 constexpr int kBK = 128;        // keys per block
 constexpr int kTile = 128 * 64 * 2;   // one [128 x 64] bf16 tile = 16 KB
-constexpr int kRing = 3;        // K / V ring slots (two CTAs of 100 KB fit one SM)
+constexpr int kRing = 4;        // K / V ring slots
+constexpr int kSBuf = 3;        // S accumulators in TMEM (128 columns each)
 constexpr int kFwdThreads = 256;
-constexpr int kFwdSmem = kTile /*Q*/ + kRing * kTile + 2 * kTile /*P*/ + 256 + 1024;
-constexpr int kFwdTmemCols = 256;  // S: [0,128), O: [128,192)
+constexpr int kFwdSmem = 2 * kTile /*Q x2*/ + kRing * kTile + 2 * 2 * kTile /*P x2*/ +
+                         4 * 4096 /*O staging*/ + 256 + 1024;
+constexpr int kFwdTmemCols = 512;  // S_b: [128 b, 128 b + 128), b < 3; O: [384, 448)
+static_assert(kFwdSmem <= 227 * 1024, "shared memory budget of one CTA");
 
 struct AttnMaps {
     CUtensorMap qkv;   // [B*S, 3H] bf16, box {64, 128}
     CUtensorMap out;   // [B*S, H] bf16, box {64, 32} (store)
 };
 
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
-__global__ void __launch_bounds__(kFwdThreads, 2)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, int S, int H,
-                int heads, float scale_log2e) {
+                int heads, int n_items, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t* sq = smem;
-    uint8_t* sring = sq + kTile;
-    uint8_t* sp = sring + kRing * kTile;
-    uint64_t* bars = (uint64_t*)(sp + 2 * kTile);
-    uint64_t* q_full = bars;
-    uint64_t* r_full = bars + 1;            // [kRing]
-    uint64_t* r_empty = r_full + kRing;     // [kRing]
-    uint64_t* s_full = r_empty + kRing;     // MMA -> softmax: S ready
-    uint64_t* s_free = s_full + 1;          // softmax -> MMA: S read (pass 1) / P written (pass 2)
-    uint64_t* pv_done = s_free + 1;         // MMA -> softmax: P V finished reading P
-    uint32_t* tmem_slot = (uint32_t*)(pv_done + 1);
+    uint8_t* sq = smem;                          // 2 x Q tile
+    uint8_t* sring = sq + 2 * kTile;             // K / V ring
+    uint8_t* sp = sring + kRing * kTile;         // 2 x P tile (2 boxes of 64 keys each)
+    uint8_t* sstage = sp + 4 * kTile;            // 4 x 4 KB O staging
+    uint64_t* bars = (uint64_t*)(sstage + 4 * 4096);
+    uint64_t* q_full = bars;                     // [2]
+    uint64_t* q_empty = q_full + 2;              // [2]
+    uint64_t* r_full = q_empty + 2;              // [kRing]
+    uint64_t* r_empty = r_full + kRing;          // [kRing]
+    uint64_t* s_full = r_empty + kRing;          // [kSBuf] MMA -> softmax
+    uint64_t* s_free = s_full + kSBuf;           // [kSBuf] softmax -> MMA (S read)
+    uint64_t* p_full = s_free + kSBuf;           // [2] softmax -> MMA (P written)
+    uint64_t* p_free = p_full + 2;               // [2] MMA -> softmax (P V has read P)
+    uint64_t* o_done = p_free + 2;               // MMA -> softmax: O of this tile complete
+    uint64_t* o_free = o_done + 1;               // softmax -> MMA: O read out
+    uint32_t* tmem_slot = (uint32_t*)(o_free + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qb = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
-    const int row0 = b * S + qb * kBQ;      // first query row of this CTA in [B*S, ...]
-    const int nkb = S / kBK;
+    const int nkb = S / kBK, nqb = S / kBQ;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.qkv) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&maps.out) : "memory");
     }
     if (warp == 1 && lane == 0) {
-        mbar_init(q_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&q_full[i], 1);
+            mbar_init(&q_empty[i], 1);
+            mbar_init(&p_full[i], 4);
+            mbar_init(&p_free[i], 1);
+        }
         for (int i = 0; i < kRing; ++i) {
             mbar_init(&r_full[i], 1);
             mbar_init(&r_empty[i], 1);
         }
-        mbar_init(s_full, 1);
-        mbar_init(s_free, 4);
-        mbar_init(pv_done, 1);
+        for (int i = 0; i < kSBuf; ++i) {
+            mbar_init(&s_full[i], 1);
+            mbar_init(&s_free[i], 4);
+        }
+        mbar_init(o_done, 1);
+        mbar_init(o_free, 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -85,29 +107,43 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, 
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 128u;
+    const uint32_t tmem_o = tmem_base + 384u;
+
+    // tile -> (batch, head, query block); query blocks of one (batch, head) are neighbours, so
+    // the CTAs working on them at the same time share its K / V through L2
+    auto decode = [&](int w, int& b, int& head, int& qb) {
+        qb = w % nqb;
+        const int t = w / nqb;
+        head = t % heads;
+        b = t / heads;
+    };
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (elect_one()) {
-            mbar_expect_tx(q_full, kTile);
-            tma_load_2d(&maps.qkv, q_full, sq, head * kD, row0);
-            const int n_loads = 3 * nkb;   // pass 1: K_j; pass 2: K_j, V_j interleaved
-            for (int li = 0; li < n_loads; ++li) {
-                const int slot = li % kRing;
-                const uint32_t ph = (uint32_t)(li / kRing) & 1u;
-                int j, which;              // which: 1 = K, 2 = V (column block of qkv)
-                if (li < nkb) {
-                    j = li;
-                    which = 1;
-                } else {
-                    j = (li - nkb) >> 1;
-                    which = 1 + ((li - nkb) & 1);
-                }
-                mbar_wait(&r_empty[slot], ph ^ 1u);
+            uint32_t L = 0;
+            auto load_kv = [&](int which, int b, int head, int j) {
+                const int slot = (int)(L % kRing);
+                mbar_wait(&r_empty[slot], ((L / kRing) & 1u) ^ 1u);
                 mbar_expect_tx(&r_full[slot], kTile);
                 tma_load_2d(&maps.qkv, &r_full[slot], sring + slot * kTile, which * H + head * kD,
                             b * S + j * kBK);
+                ++L;
+            };
+            int it = 0;
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+                int b, head, qb;
+                decode(w, b, head, qb);
+                const int qs = it & 1;
+                mbar_wait(&q_empty[qs], (((uint32_t)it >> 1) & 1u) ^ 1u);
+                mbar_expect_tx(&q_full[qs], kTile);
+                tma_load_2d(&maps.qkv, &q_full[qs], sq + qs * kTile, head * kD, b * S + qb * kBQ);
+                for (int j = 0; j < nkb; ++j) load_kv(1, b, head, j);          // pass 1
+                for (int j = 0; j < 2 && j < nkb; ++j) load_kv(1, b, head, j); // pass 2 runs 2 ahead
+                for (int j = 0; j < nkb; ++j) {
+                    if (j + 2 < nkb) load_kv(1, b, head, j + 2);
+                    load_kv(2, b, head, j);
+                }
             }
         }
     } else if (warp == 1) {
@@ -115,144 +151,163 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, 
         if (elect_one()) {
             const uint32_t idesc_s = make_idesc(kBQ, kBK);                   // S = Q K^T
             const uint32_t idesc_o = make_idesc_major(kBQ, kD, 0, 1);        // O += P V (V MN-major)
-            const uint32_t q_addr = smem_u32(sq), p_addr = smem_u32(sp);
-            mbar_wait(q_full, 0);
-            tcgen05_fence_after();
-            int li = 0;
-            uint32_t sf = 0;              // s_free completions consumed so far
-            bool owe = false;             // a previous S has not been waited free yet
-            auto issue_s = [&](int slot) {
-                const uint32_t k_addr = smem_u32(sring + slot * kTile);
-#pragma unroll
-                for (int k = 0; k < kD / UMMA_K; ++k)
-                    umma_bf16(tmem_s, make_smem_desc(q_addr + k * 32), make_smem_desc(k_addr + k * 32),
-                              idesc_s, k != 0 ? 1u : 0u);
-                umma_commit(&r_empty[slot]);
-                umma_commit(s_full);
-            };
-            for (int pass = 0; pass < 2; ++pass)
-                for (int j = 0; j < nkb; ++j) {
-                    int slot = li % kRing;
-                    mbar_wait(&r_full[slot], (uint32_t)(li / kRing) & 1u);
-                    if (owe) {
-                        mbar_wait(s_free, sf & 1u);
-                        ++sf;
-                    }
+            uint32_t L = 0, T = 0, J = 0;    // ring loads / S tiles / P V products consumed so far
+            int it = 0;
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+                const int qs = it & 1;
+                mbar_wait(&q_full[qs], ((uint32_t)it >> 1) & 1u);
+                tcgen05_fence_after();
+                const uint32_t q_addr = smem_u32(sq + qs * kTile);
+                auto issue_s = [&]() {
+                    const int slot = (int)(L % kRing);
+                    mbar_wait(&r_full[slot], (L / kRing) & 1u);
+                    const int sb = (int)(T % kSBuf);
+                    if (T >= kSBuf) mbar_wait(&s_free[sb], ((T / kSBuf) - 1u) & 1u);
                     tcgen05_fence_after();
-                    issue_s(slot);
-                    owe = true;
-                    ++li;
-                    if (pass == 1) {
-                        slot = li % kRing;
-                        mbar_wait(&r_full[slot], (uint32_t)(li / kRing) & 1u);   // V_j
-                        mbar_wait(s_free, sf & 1u);                              // P_j written
-                        ++sf;
-                        owe = false;
-                        tcgen05_fence_after();
-                        const uint32_t v_addr = smem_u32(sring + slot * kTile);
+                    const uint32_t k_addr = smem_u32(sring + slot * kTile);
 #pragma unroll
-                        for (int k = 0; k < kBK / UMMA_K; ++k) {
-                            // P: two K-major boxes of 64 keys; V: 128 key rows of 128 bytes
-                            const uint32_t pa = p_addr + (k >> 2) * kTile + (k & 3) * 32;
-                            umma_bf16(tmem_o, make_smem_desc(pa), make_smem_desc_mn(v_addr + k * 2048),
-                                      idesc_o, (j | k) != 0 ? 1u : 0u);
-                        }
-                        umma_commit(&r_empty[slot]);
-                        umma_commit(pv_done);
-                        ++li;
+                    for (int k = 0; k < kD / UMMA_K; ++k)
+                        umma_bf16(tmem_base + (uint32_t)(sb * 128), make_smem_desc(q_addr + k * 32),
+                                  make_smem_desc(k_addr + k * 32), idesc_s, k != 0 ? 1u : 0u);
+                    umma_commit(&r_empty[slot]);
+                    umma_commit(&s_full[sb]);
+                    ++L;
+                    ++T;
+                };
+                for (int j = 0; j < nkb; ++j) issue_s();
+                for (int j = 0; j < 2 && j < nkb; ++j) issue_s();
+                for (int j = 0; j < nkb; ++j) {
+                    if (j + 2 < nkb) issue_s();
+                    const int slot = (int)(L % kRing);
+                    mbar_wait(&r_full[slot], (L / kRing) & 1u);                  // V_j
+                    const int pb = (int)(J & 1u);
+                    mbar_wait(&p_full[pb], (J >> 1) & 1u);                       // P_j written
+                    if (j == 0 && it > 0) mbar_wait(o_free, (uint32_t)(it - 1) & 1u);
+                    tcgen05_fence_after();
+                    const uint32_t v_addr = smem_u32(sring + slot * kTile);
+                    const uint32_t p_addr = smem_u32(sp + pb * 2 * kTile);
+#pragma unroll
+                    for (int k = 0; k < kBK / UMMA_K; ++k) {
+                        // P: two K-major boxes of 64 keys; V: 128 key rows of 128 bytes
+                        const uint32_t pa = p_addr + (k >> 2) * kTile + (k & 3) * 32;
+                        umma_bf16(tmem_o, make_smem_desc(pa), make_smem_desc_mn(v_addr + k * 2048),
+                                  idesc_o, (j | k) != 0 ? 1u : 0u);
                     }
+                    umma_commit(&r_empty[slot]);
+                    umma_commit(&p_free[pb]);
+                    ++L;
+                    ++J;
                 }
+                umma_commit(o_done);
+                umma_commit(&q_empty[qs]);
+            }
         }
     } else if (warp >= kEpiWarp0) {
         // ===================== softmax: one thread per query row =====================
         const int ew = warp - kEpiWarp0;
         const int row = ew * 32 + lane;
-        const uint32_t t_s = tmem_s + ((uint32_t)(ew * 32) << 16);
-        const uint32_t t_o = tmem_o + ((uint32_t)(ew * 32) << 16);
-        uint32_t n_s = 0;                 // s_full completions consumed
-        float m = -INFINITY;
-        for (int j = 0; j < nkb; ++j) {   // pass 1: exact row maximum
-            mbar_wait(s_full, n_s & 1u);
-            ++n_s;
-            tcgen05_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < kBK; c += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(t_s + (uint32_t)c, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) m = fmaxf(m, __uint_as_float(r[i]));
-            }
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(s_free);
-        }
-        const float mc = m * scale_log2e;
-        float l = 0.f;
+        const uint32_t lane_sel = (uint32_t)(ew * 32) << 16;
         const uint32_t sw = (uint32_t)(row & 7);
-        uint8_t* prow = sp + (uint32_t)row * 128u;
-        for (int j = 0; j < nkb; ++j) {   // pass 2: probabilities
-            mbar_wait(s_full, n_s & 1u);
-            ++n_s;
-            tcgen05_fence_after();
+        uint8_t* obox = sstage + ew * 4096;
+        uint32_t T = 0, J = 0;
+        int it = 0;
+        for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+            int b, head, qb;
+            decode(w, b, head, qb);
+            float m = -INFINITY;
+            for (int j = 0; j < nkb; ++j, ++T) {   // pass 1: exact row maximum
+                const int sb = (int)(T % kSBuf);
+                mbar_wait(&s_full[sb], (T / kSBuf) & 1u);
+                tcgen05_fence_after();
+                const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
 #pragma unroll 1
-            for (int c = 0; c < kBK; c += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(t_s + (uint32_t)c, r);
-                tmem_ld_wait();
-                uint32_t pk[16];
+                for (int c = 0; c < kBK; c += 64) {
+                    uint32_t r0[32], r1[32];
+                    tmem_ld_32x32b_x32(t_s + (uint32_t)c, r0);
+                    tmem_ld_32x32b_x32(t_s + (uint32_t)c + 32u, r1);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const float p0 = exp2f(fmaf(__uint_as_float(r[2 * i]), scale_log2e, -mc));
-                    const float p1 = exp2f(fmaf(__uint_as_float(r[2 * i + 1]), scale_log2e, -mc));
-                    const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
-                    // the row sum is that of the ROUNDED probabilities the tensor core will use
-                    const float2 back = __bfloat1622float2(h2);
-                    l += back.x + back.y;
-                    pk[i] = *reinterpret_cast<const uint32_t*>(&h2);
+                    for (int i = 0; i < 32; ++i)
+                        m = fmaxf(m, fmaxf(__uint_as_float(r0[i]), __uint_as_float(r1[i])));
                 }
-                if (c == 0 && j > 0) mbar_wait(pv_done, (uint32_t)(j - 1) & 1u);   // P buffer free
-                uint8_t* box = prow + (c >> 6) * kTile;      // keys 0-63 | 64-127
-                const uint32_t ch0 = (uint32_t)(c & 63) >> 3;  // first 16-byte chunk: 0 or 4
-#pragma unroll
-                for (uint32_t q = 0; q < 4; ++q)
-                    *reinterpret_cast<uint4*>(box + (((ch0 + q) ^ sw) << 4)) =
-                        make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_free[sb]);
             }
-            tcgen05_fence_before();
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(s_free);
-        }
-        // ---- O / l -> bf16 -> swizzled box (the P tile is free now) -> TMA store; lse ----
-        mbar_wait(pv_done, (uint32_t)(nkb - 1) & 1u);
-        tcgen05_fence_after();
-        const float inv = 1.f / l;
-        uint8_t* obox = sp + ew * 4096;
+            const float mc = m * scale_log2e;
+            float l = 0.f;
+            for (int j = 0; j < nkb; ++j, ++T, ++J) {   // pass 2: probabilities
+                const int sb = (int)(T % kSBuf);
+                const int pb = (int)(J & 1u);
+                mbar_wait(&s_full[sb], (T / kSBuf) & 1u);
+                tcgen05_fence_after();
+                const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
+                uint8_t* prow = sp + pb * 2 * kTile + (uint32_t)row * 128u;
 #pragma unroll 1
-        for (int c = 0; c < kD; c += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(t_o + (uint32_t)c, r);
+                for (int c = 0; c < kBK; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(t_s + (uint32_t)c, r);
+                    tmem_ld_wait();
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float p0 = ex2_approx(fmaf(__uint_as_float(r[2 * i]), scale_log2e, -mc));
+                        const float p1 = ex2_approx(fmaf(__uint_as_float(r[2 * i + 1]), scale_log2e, -mc));
+                        l += p0 + p1;
+                        const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+                        pk[i] = *reinterpret_cast<const uint32_t*>(&h2);
+                    }
+                    // the P V product that last read this P buffer must have finished
+                    if (c == 0 && J >= 2) mbar_wait(&p_free[pb], ((J >> 1) - 1u) & 1u);
+                    uint8_t* box = prow + (c >> 6) * kTile;      // keys 0-63 | 64-127
+                    const uint32_t ch0 = (uint32_t)(c & 63) >> 3;  // first 16-byte chunk: 0 or 4
+#pragma unroll
+                    for (uint32_t q = 0; q < 4; ++q)
+                        *reinterpret_cast<uint4*>(box + (((ch0 + q) ^ sw) << 4)) =
+                            make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                }
+                tcgen05_fence_before();
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&s_free[sb]);
+                    mbar_arrive(&p_full[pb]);
+                }
+            }
+            // ---- O / l -> bf16 -> swizzled box -> TMA store; lse ----
+            mbar_wait(o_done, (uint32_t)it & 1u);
+            tcgen05_fence_after();
+            uint32_t ro[64];
+            tmem_ld_32x32b_x32(tmem_o + lane_sel, ro);
+            tmem_ld_32x32b_x32(tmem_o + lane_sel + 32u, ro + 32);
             tmem_ld_wait();
-            float f[32];
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(o_free);
+                bulk_wait_read<0>();          // the previous tile's store has drained the box
+            }
+            __syncwarp();
+            const float inv = 1.f / l;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]) * inv;
+            for (int q = 0; q < 8; ++q) {
+                float f[8];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                bf16x8 v = f32_to_bf16x8(f + 8 * q);
+                for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(ro[8 * q + i]) * inv;
+                bf16x8 v = f32_to_bf16x8(f);
                 *reinterpret_cast<uint4*>(obox + (uint32_t)lane * 128u +
-                                          ((((uint32_t)(c >> 3) + q) ^ (uint32_t)(lane & 7)) << 4)) =
+                                          (((uint32_t)q ^ (uint32_t)(lane & 7)) << 4)) =
                     *reinterpret_cast<uint4*>(&v);
             }
+            lse[((size_t)b * heads + head) * S + qb * kBQ + row] = mc + log2f(l);
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&maps.out, obox, head * kD, b * S + qb * kBQ + ew * 32);
+                bulk_commit();
+            }
         }
-        lse[((size_t)b * heads + head) * S + qb * kBQ + row] = mc + log2f(l);
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-            tma_store_2d(&maps.out, obox, head * kD, row0 + ew * 32);
-            bulk_commit();
-            bulk_wait_read<0>();
-        }
+        if (lane == 0) bulk_wait_read<0>();
         __syncwarp();
     }
 
@@ -278,6 +333,9 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, 
 //   dK_j += dS^T Q_i            A = dS^T (K-major)   B = Q_i  (MN-major, as stored)
 //   dQ_i  = dS   K_j            A = dS^T read MN-major (it IS dS stored [key][query])
 //                                                    B = K_j  (MN-major, as stored)
+// Each query block is processed as two halves of 64 queries that ping-pong between the tensor core
+// and the threads (the first version, whole blocks in strict MMA -> threads -> MMA turns, kept
+// the tensor pipe 14 % and the issue slots 21 % busy).
 // dV_j / dK_j accumulate in TMEM over i and leave through TMA stores into the packed gradient
 // dqkv[B*S, 3H]; the dQ_i tiles of the S/128 CTAs of one (batch, head) meet in an fp32 buffer by
 // TMA reduce-add (attn_dq_convert_kernel rounds it into dqkv afterwards).
@@ -323,10 +381,11 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
     uint64_t* kv_full = bars;
     uint64_t* qd_full = bars + 1;           // [2]
     uint64_t* qd_empty = qd_full + 2;       // [2]
-    uint64_t* s_full = qd_empty + 2;        // MMA -> threads: S^T and dP^T of block i ready
-    uint64_t* p_ready = s_full + 1;         // threads -> MMA: P^T / dS^T written, S^T / dP^T / dQ read
-    uint64_t* mma2_done = p_ready + 1;      // MMA -> threads: dV, dK, dQ_i products of block i done
-    uint32_t* tmem_slot = (uint32_t*)(mma2_done + 1);
+    uint64_t* st_full = qd_empty + 2;       // [2] MMA -> threads: S^T / dP^T of half h ready
+    uint64_t* st_free = st_full + 2;        // [2] threads -> MMA: that half has been read
+    uint64_t* pt_full = st_free + 2;        // [2] threads -> MMA: P^T / dS^T box h written
+    uint64_t* g2_done = pt_full + 2;        // MMA -> threads: dV, dK, dQ products of block i done
+    uint32_t* tmem_slot = (uint32_t*)(g2_done + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int jb = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
@@ -344,10 +403,11 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
         for (int i = 0; i < 2; ++i) {
             mbar_init(&qd_full[i], 1);
             mbar_init(&qd_empty[i], 1);
+            mbar_init(&st_full[i], 1);
+            mbar_init(&st_free[i], 4);
+            mbar_init(&pt_full[i], 4);
         }
-        mbar_init(s_full, 1);
-        mbar_init(p_ready, 4);
-        mbar_init(mma2_done, 1);
+        mbar_init(g2_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -382,43 +442,58 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (elect_one()) {
-            const uint32_t id_s = make_idesc(128, 128);                 // both K-major
+            const uint32_t id_s = make_idesc(128, 64);                  // both K-major, 64 queries
             const uint32_t id_acc = make_idesc_major(128, kD, 0, 1);    // A K-major, B MN-major
             const uint32_t id_dq = make_idesc_major(128, kD, 1, 1);     // both MN-major
             const uint32_t k_addr = smem_u32(sk), v_addr = smem_u32(sv);
             const uint32_t pt_addr = smem_u32(spt), dst_addr = smem_u32(sdst);
             mbar_wait(kv_full, 0);
+            // S^T / dP^T of one HALF (64 queries) of block i: the halves ping-pong, so the
+            // threads work on one while the tensor core produces the other
+            auto issue_s = [&](int i, int h) {
+                const int st = i & 1;
+                if (h == 0) mbar_wait(&qd_full[st], (uint32_t)(i >> 1) & 1u);
+                if (i > 0) mbar_wait(&st_free[h], (uint32_t)(i - 1) & 1u);
+                tcgen05_fence_after();
+                const uint32_t q_addr = smem_u32(sqd + st * 2 * kTile) + h * 8192, do_addr = q_addr + kTile;
+#pragma unroll
+                for (int k = 0; k < kD / UMMA_K; ++k)
+                    umma_bf16(t_st + (uint32_t)(h * 64), make_smem_desc(k_addr + k * 32),
+                              make_smem_desc(q_addr + k * 32), id_s, k != 0 ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < kD / UMMA_K; ++k)
+                    umma_bf16(t_dpt + (uint32_t)(h * 64), make_smem_desc(v_addr + k * 32),
+                              make_smem_desc(do_addr + k * 32), id_s, k != 0 ? 1u : 0u);
+                umma_commit(&st_full[h]);
+            };
+            issue_s(0, 0);
+            issue_s(0, 1);
             for (int i = 0; i < nqb; ++i) {
                 const int st = i & 1;
-                mbar_wait(&qd_full[st], (uint32_t)(i >> 1) & 1u);
-                tcgen05_fence_after();
                 const uint32_t q_addr = smem_u32(sqd + st * 2 * kTile), do_addr = q_addr + kTile;
+                for (int h = 0; h < 2; ++h) {
+                    mbar_wait(&pt_full[h], (uint32_t)i & 1u);
+                    tcgen05_fence_after();
 #pragma unroll
-                for (int k = 0; k < kD / UMMA_K; ++k)
-                    umma_bf16(t_st, make_smem_desc(k_addr + k * 32), make_smem_desc(q_addr + k * 32),
-                              id_s, k != 0 ? 1u : 0u);
+                    for (int k = 0; k < 64 / UMMA_K; ++k) {
+                        // K-major A: box h holds queries h*64 .. h*64+63; MN-major B: those rows
+                        const uint32_t aoff = h * kTile + k * 32, boff = h * 8192 + k * 2048;
+                        umma_bf16(t_dv, make_smem_desc(pt_addr + aoff), make_smem_desc_mn(do_addr + boff),
+                                  id_acc, (i | h | k) != 0 ? 1u : 0u);
+                        umma_bf16(t_dk, make_smem_desc(dst_addr + aoff), make_smem_desc_mn(q_addr + boff),
+                                  id_acc, (i | h | k) != 0 ? 1u : 0u);
+                    }
+                    if (h == 1) {
 #pragma unroll
-                for (int k = 0; k < kD / UMMA_K; ++k)
-                    umma_bf16(t_dpt, make_smem_desc(v_addr + k * 32), make_smem_desc(do_addr + k * 32),
-                              id_s, k != 0 ? 1u : 0u);
-                umma_commit(s_full);
-                mbar_wait(p_ready, (uint32_t)i & 1u);
-                tcgen05_fence_after();
-#pragma unroll
-                for (int k = 0; k < 128 / UMMA_K; ++k) {
-                    // K-major A tiles: two 64-query boxes; MN-major B: 128 rows of 128 bytes
-                    const uint32_t aoff = (k >> 2) * kTile + (k & 3) * 32;
-                    umma_bf16(t_dv, make_smem_desc(pt_addr + aoff), make_smem_desc_mn(do_addr + k * 2048),
-                              id_acc, (i | k) != 0 ? 1u : 0u);
-                    umma_bf16(t_dk, make_smem_desc(dst_addr + aoff), make_smem_desc_mn(q_addr + k * 2048),
-                              id_acc, (i | k) != 0 ? 1u : 0u);
+                        for (int k = 0; k < 128 / UMMA_K; ++k)
+                            umma_bf16(t_dq, make_smem_desc_mn_lbo(dst_addr + k * 2048, kTile),
+                                      make_smem_desc_mn(k_addr + k * 2048), id_dq, k != 0 ? 1u : 0u);
+                        umma_commit(&qd_empty[st]);
+                        umma_commit(g2_done);
+                    }
+                    // the next block's half h: its S^T / dP^T columns were read before pt_full[h]
+                    if (i + 1 < nqb) issue_s(i + 1, h);
                 }
-#pragma unroll
-                for (int k = 0; k < 128 / UMMA_K; ++k)
-                    umma_bf16(t_dq, make_smem_desc_mn_lbo(dst_addr + k * 2048, kTile),
-                              make_smem_desc_mn(k_addr + k * 2048), id_dq, k != 0 ? 1u : 0u);
-                umma_commit(&qd_empty[st]);
-                umma_commit(mma2_done);
             }
         }
     } else if (warp >= kEpiWarp0) {
@@ -457,47 +532,58 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
             vec[row] = lse[vec0 + i * kBQ + row];
             vec[128 + row] = delta[vec0 + i * kBQ + row];
             epi_bar_sync();
-            mbar_wait(s_full, (uint32_t)i & 1u);
-            tcgen05_fence_after();
-            // dQ of the previous query block (its MMAs precede this block's S^T in issue order)
-            if (i > 0) flush_f32(t_dq, head * kD, b * S + (i - 1) * kBQ + ew * 32);
-#pragma unroll 1
-            for (int c = 0; c < kBQ; c += 32) {
-                uint32_t rs[32], rd[32];
-                tmem_ld_32x32b_x32(t_st + lane_sel + (uint32_t)c, rs);
-                tmem_ld_32x32b_x32(t_dpt + lane_sel + (uint32_t)c, rd);
-                tmem_ld_wait();
-                uint32_t pk[16], dk[16];
-#pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    const float2 l2 = *reinterpret_cast<const float2*>(vec + c + 2 * k);
-                    const float2 d2 = *reinterpret_cast<const float2*>(vec + 128 + c + 2 * k);
-                    const float p0 = exp2f(fmaf(__uint_as_float(rs[2 * k]), scale_log2e, -l2.x));
-                    const float p1 = exp2f(fmaf(__uint_as_float(rs[2 * k + 1]), scale_log2e, -l2.y));
-                    const float s0 = p0 * (__uint_as_float(rd[2 * k]) - d2.x) * scale;
-                    const float s1 = p1 * (__uint_as_float(rd[2 * k + 1]) - d2.y) * scale;
-                    const __nv_bfloat162 ph = __floats2bfloat162_rn(p0, p1);
-                    const __nv_bfloat162 dh = __floats2bfloat162_rn(s0, s1);
-                    pk[k] = *reinterpret_cast<const uint32_t*>(&ph);
-                    dk[k] = *reinterpret_cast<const uint32_t*>(&dh);
+            for (int h = 0; h < 2; ++h) {
+                mbar_wait(&st_full[h], (uint32_t)i & 1u);
+                tcgen05_fence_after();
+                if (h == 0 && i > 0) {
+                    // block i-1 is finished on the tensor core: its dQ tile can leave, and the
+                    // P^T / dS^T boxes may be overwritten
+                    mbar_wait(g2_done, (uint32_t)(i - 1) & 1u);
+                    tcgen05_fence_after();
+                    flush_f32(t_dq, head * kD, b * S + (i - 1) * kBQ + ew * 32);
                 }
-                const uint32_t boff = (uint32_t)(c >> 6) * kTile;
-                const uint32_t ch0 = (uint32_t)(c & 63) >> 3;
+#pragma unroll 1
+                for (int c = 0; c < 64; c += 32) {
+                    const int qc = h * 64 + c;              // query column inside the block
+                    uint32_t rs[32], rd[32];
+                    tmem_ld_32x32b_x32(t_st + lane_sel + (uint32_t)qc, rs);
+                    tmem_ld_32x32b_x32(t_dpt + lane_sel + (uint32_t)qc, rd);
+                    tmem_ld_wait();
+                    uint32_t pk[16], dk[16];
 #pragma unroll
-                for (uint32_t q = 0; q < 4; ++q) {
-                    const uint32_t off = boff + (((ch0 + q) ^ sw) << 4);
-                    *reinterpret_cast<uint4*>(ptrow + off) =
-                        make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-                    *reinterpret_cast<uint4*>(dstrow + off) =
-                        make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+                    for (int k = 0; k < 16; ++k) {
+                        const float2 l2 = *reinterpret_cast<const float2*>(vec + qc + 2 * k);
+                        const float2 d2 = *reinterpret_cast<const float2*>(vec + 128 + qc + 2 * k);
+                        const float p0 = ex2_approx(fmaf(__uint_as_float(rs[2 * k]), scale_log2e, -l2.x));
+                        const float p1 = ex2_approx(fmaf(__uint_as_float(rs[2 * k + 1]), scale_log2e, -l2.y));
+                        const float s0 = p0 * (__uint_as_float(rd[2 * k]) - d2.x) * scale;
+                        const float s1 = p1 * (__uint_as_float(rd[2 * k + 1]) - d2.y) * scale;
+                        const __nv_bfloat162 ph = __floats2bfloat162_rn(p0, p1);
+                        const __nv_bfloat162 dh = __floats2bfloat162_rn(s0, s1);
+                        pk[k] = *reinterpret_cast<const uint32_t*>(&ph);
+                        dk[k] = *reinterpret_cast<const uint32_t*>(&dh);
+                    }
+                    const uint32_t boff = (uint32_t)h * kTile;
+                    const uint32_t ch0 = (uint32_t)c >> 3;
+#pragma unroll
+                    for (uint32_t q = 0; q < 4; ++q) {
+                        const uint32_t off = boff + (((ch0 + q) ^ sw) << 4);
+                        *reinterpret_cast<uint4*>(ptrow + off) =
+                            make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                        *reinterpret_cast<uint4*>(dstrow + off) =
+                            make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+                    }
+                }
+                tcgen05_fence_before();
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&st_free[h]);
+                    mbar_arrive(&pt_full[h]);
                 }
             }
-            tcgen05_fence_before();
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(p_ready);
         }
-        mbar_wait(mma2_done, (uint32_t)(nqb - 1) & 1u);
+        mbar_wait(g2_done, (uint32_t)(nqb - 1) & 1u);
         tcgen05_fence_after();
         flush_f32(t_dq, head * kD, b * S + (nqb - 1) * kBQ + ew * 32);
         // dV_j, dK_j: fp32 TMEM -> bf16 -> swizzled box -> TMA store into the packed gradient
@@ -659,8 +745,12 @@ TFOP_API int tfop_attn_fwd(const void* qkv, void* out, float* lse, int B, int S,
     TFOP_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    kFwdSmem));
     const float scale_log2e = 0.125f * 1.4426950408889634f;
-    attn_fwd_kernel<<<dim3(S / kBQ, heads, B), kFwdThreads, kFwdSmem, stream>>>(maps, lse, S, H,
-                                                                                 heads, scale_log2e);
+    int dev = 0, sms = 0;
+    TFOP_CUDA(cudaGetDevice(&dev));
+    TFOP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int n_items = B * heads * (S / kBQ);
+    attn_fwd_kernel<<<n_items < sms ? n_items : sms, kFwdThreads, kFwdSmem, stream>>>(
+        maps, lse, S, H, heads, n_items, scale_log2e);
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }
