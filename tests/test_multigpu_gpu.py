@@ -71,6 +71,9 @@ def test_collective_kernels_on_real_peer_mappings(cluster, tmp_path):
                      ["python", "tests/workers/multigpu_kernels.py", str(out)])
     run_job(cluster, job)
     res = [json.load(open(f)) for f in sorted(glob.glob(str(out / "rank*.json")))]
+    if os.path.isdir(os.path.join(REPO, "gpurun_out")):       # keep the per-rank records of a GPU run
+        with open(os.path.join(REPO, "gpurun_out", f"multigpu_kernels_{WORLD}gpu.json"), "w") as f:
+            json.dump(res, f, indent=1)
     assert len(res) == WORLD and all(r["world"] == WORLD for r in res)
     names = set(res[0]["checks"])
     assert {"p2p_oneshot_bfloat16_1000", "p2p_twoshot_float32_262168", "p2p_twoshot_inplace_bf16",
@@ -79,9 +82,9 @@ def test_collective_kernels_on_real_peer_mappings(cluster, tmp_path):
         assert {"nvls_outofplace_bfloat16", "nvls_inplace_bf16", "nvls_inplace_bf16_second_call",
                 "gemm_allreduce_nvls"} <= names
     for r in res:
-        assert not r["error_word"]
-        bad = {k: v for k, v in r["checks"].items() if not v["ok"]}
+        bad = {k: v for k, v in r["checks"].items() if not v["ok"] or v["error_word_after"]}
         assert not bad, (r["rank"], bad)
+        assert not r["error_word"]
         assert set(r["checks"]) == names
     # every rank holds the same bits
     for k in names:

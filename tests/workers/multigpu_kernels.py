@@ -42,7 +42,8 @@ def main():
         torch.cuda.synchronize()
         err = (got.float() - want).abs().max().item()
         tol = atol + rtol * want.abs().max().item()
-        res["checks"][name] = {"max_err": err, "tol": tol, "ok": bool(err <= tol), "sha1": digest(got)}
+        res["checks"][name] = {"max_err": err, "tol": tol, "ok": bool(err <= tol), "sha1": digest(got),
+                               "error_word_after": bool(comm.check_error())}
 
     seed = 0
     # ---- P2P one-shot / two-shot, bf16 and fp32 wire, out of place --------------------------
@@ -102,20 +103,31 @@ def main():
         want += ar.float() @ br.float().t()
     ws = SymmetricComm.gemm_allreduce_workspace_bytes(m, nn, W)
     out_off = (ws + 255) // 256 * 256
-    torch.cuda.synchronize()
-    comm._exit_barrier()
+
+    def fresh_workspace():
+        # the fused kernels' workspace (partial-tile slots + monotone arrival counters) must start
+        # at zero and serve ONE (M, N, world) and one flavour; the collectives
+        # above used the same bytes as staging. Every rank zeroes its own, then all meet.
+        torch.cuda.synchronize()
+        comm._exit_barrier()
+        comm.view(0, out_off, torch.uint8).zero_()
+        torch.cuda.synchronize()
+        comm._exit_barrier()
+
+    fresh_workspace()
     got = comm.gemm_all_reduce(a, b, ws_off=0, out_off=out_off)
     record("gemm_allreduce_p2p", got, want, 2e-2, 2e-2)
     if comm.nvls_bytes:
-        torch.cuda.synchronize()
-        comm._exit_barrier()
+        fresh_workspace()
         got = comm.gemm_all_reduce_nvls(a, b, ws_off=0, out_off=0)
         record("gemm_allreduce_nvls", got, want, 2e-2, 2e-2)
     res["error_word"] = comm.check_error()
     with open(os.path.join(out_dir, f"rank{R}.json"), "w") as f:
         json.dump(res, f)
     assert comm.close()
-    print(f"rank {R}: {sum(c['ok'] for c in res['checks'].values())}/{len(res['checks'])} checks ok", flush=True)
+    bad = {k: v for k, v in res["checks"].items() if not v["ok"]}
+    print(f"rank {R}: {len(res['checks']) - len(bad)}/{len(res['checks'])} checks ok; "
+          f"error_word={res['error_word']}; failed: {json.dumps(bad)}", flush=True)
 
 
 if __name__ == "__main__":

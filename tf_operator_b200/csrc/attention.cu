@@ -339,10 +339,10 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, 
 // dV_j / dK_j accumulate in TMEM over i and leave through TMA stores into the packed gradient
 // dqkv[B*S, 3H]; the dQ_i tiles of the S/128 CTAs of one (batch, head) meet in an fp32 buffer by
 // TMA reduce-add (attn_dq_convert_kernel rounds it into dqkv afterwards).
-constexpr int kBwdThreads = 256;
+constexpr int kBwdThreads = 384;   // warps 0-3 as in the GEMM, 4-7 / 8-11: one thread group per half
 constexpr int kBwdTmemCols = 512;   // S^T [0,128) dP^T [128,256) dV [256,320) dK [320,384) dQ [384,448)
 constexpr int kBwdSmem = 2 * kTile /*K V*/ + 4 * kTile /*Q dO x2*/ + 2 * kTile /*P^T*/ +
-                         2 * kTile /*dS^T*/ + 4 * 4096 /*staging*/ + 2 * 2 * 512 /*lse delta*/ +
+                         2 * kTile /*dS^T*/ + 8 * 4096 /*staging*/ + 2 * 2 * 512 /*lse delta*/ +
                          256 + 1024;
 static_assert(kBwdSmem <= 227 * 1024, "shared memory budget of one CTA");
 
@@ -376,7 +376,7 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
     uint8_t* spt = sqd + 4 * kTile;         // P^T   [128 keys][128 queries] as two 64-query boxes
     uint8_t* sdst = spt + 2 * kTile;        // dS^T  same layout
     uint8_t* sstage = sdst + 2 * kTile;     // 4 x 4 KB store staging
-    float* svec = (float*)(sstage + 4 * 4096);   // [2 stages][lse | delta][128]
+    float* svec = (float*)(sstage + 8 * 4096);   // [2 stages][lse | delta][128]
     uint64_t* bars = (uint64_t*)((uint8_t*)svec + 2 * 2 * 512);
     uint64_t* kv_full = bars;
     uint64_t* qd_full = bars + 1;           // [2]
@@ -498,18 +498,22 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
         }
     } else if (warp >= kEpiWarp0) {
         // ===================== one thread per key row =====================
-        const int ew = warp - kEpiWarp0;
+        // Two groups of four warps: group h owns the 64-query half h of every block (its S^T /
+        // dP^T columns, its P^T / dS^T box), so both halves are in flight at once and every SM
+        // sub-partition has two warps to hide latencies with.
+        const int grp = (warp - kEpiWarp0) >> 2;
+        const int ew = warp & 3;                     // TMEM lane quadrant
         const int row = ew * 32 + lane;
         const uint32_t lane_sel = (uint32_t)(ew * 32) << 16;
         const uint32_t sw = (uint32_t)(row & 7);
         uint8_t* ptrow = spt + (uint32_t)row * 128u;
         uint8_t* dstrow = sdst + (uint32_t)row * 128u;
-        uint8_t* stage = sstage + ew * 4096;
+        uint8_t* stage = sstage + (grp * 4 + ew) * 4096;
         const size_t vec0 = ((size_t)b * heads + head) * S;
         // fp32 [32 rows x 32 cols] of a TMEM accumulator -> swizzled staging box -> TMA
         auto flush_f32 = [&](uint32_t taddr, int col, int grow) {
-#pragma unroll 1
-            for (int c = 0; c < kD; c += 32) {
+            {
+                const int c = grp * 32;              // this group's 32 of the 64 columns
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(taddr + lane_sel + (uint32_t)c, r);
                 tmem_ld_wait();
@@ -529,13 +533,16 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
         };
         for (int i = 0; i < nqb; ++i) {
             float* vec = svec + (i & 1) * 256;
-            vec[row] = lse[vec0 + i * kBQ + row];
-            vec[128 + row] = delta[vec0 + i * kBQ + row];
-            epi_bar_sync();
-            for (int h = 0; h < 2; ++h) {
+            if (grp == 0)
+                vec[row] = lse[vec0 + i * kBQ + row];
+            else
+                vec[128 + row] = delta[vec0 + i * kBQ + row];
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {
+                const int h = grp;
                 mbar_wait(&st_full[h], (uint32_t)i & 1u);
                 tcgen05_fence_after();
-                if (h == 0 && i > 0) {
+                if (i > 0) {
                     // block i-1 is finished on the tensor core: its dQ tile can leave, and the
                     // P^T / dS^T boxes may be overwritten
                     mbar_wait(g2_done, (uint32_t)(i - 1) & 1u);
@@ -587,8 +594,8 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
         tcgen05_fence_after();
         flush_f32(t_dq, head * kD, b * S + (nqb - 1) * kBQ + ew * 32);
         // dV_j, dK_j: fp32 TMEM -> bf16 -> swizzled box -> TMA store into the packed gradient
-#pragma unroll 1
-        for (int which = 0; which < 2; ++which) {
+        {
+            const int which = grp;                   // group 0 stores dV_j, group 1 dK_j
             const uint32_t taddr = (which == 0 ? t_dv : t_dk) + lane_sel;
             if (lane == 0) bulk_wait_read<0>();
             __syncwarp();
