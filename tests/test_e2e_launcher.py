@@ -252,6 +252,35 @@ def test_gang_admission_is_all_or_nothing():
         cl.stop()
 
 
+def test_pod_that_does_not_fit_waits_for_a_gpu_and_then_runs():
+    """A pod that finds no free GPU stays Pending (PodScheduled=False, Unschedulable) and is placed
+    as soon as another pod gives its GPU back - what kube-scheduler's retry queue does. The case
+    behind it: a job re-created right after its same-named predecessor was deleted, while one of
+    the old replicas was still exiting."""
+    cl = LocalCluster(topology=synthetic(1), serve_http=True,
+                      kubelet_options=KubeletOptions(cwd=REPO, gpus_per_replica_default=1))
+    try:
+        cli = TFJobClient(cluster=cl)
+        cli.create(tfjob("first", {"Worker": 1}))
+        wait_running(cl, "first", 1)
+        cli.create(tfjob("second", {"Worker": 1}))
+        pod = wait(lambda: [p for p in cl.store.list("pods", "default", "job-name=second")
+                            if (p.get("status") or {}).get("conditions")])[0]
+        cond = pod["status"]["conditions"][0]
+        assert (pod["status"]["phase"], cond["type"], cond["status"], cond["reason"]) == \
+            ("Pending", "PodScheduled", "False", "Unschedulable")
+        assert cl.kubelet.free_gpus() == []
+        http_get(cl, "first-worker-0", "exit?exitCode=0")
+        wait_running(cl, "second", 1)
+        env = json.loads(http_get(cl, "second-worker-0", "env"))
+        assert env["CUDA_VISIBLE_DEVICES"] == "0"
+        http_get(cl, "second-worker-0", "exit?exitCode=0")
+        cli.wait_for_job("second", polling_interval=0.05, timeout_seconds=30)
+        assert cli.is_job_succeeded("second") and cl.kubelet.free_gpus() == [0]
+    finally:
+        cl.stop()
+
+
 # BASELINE.json config 1 ---------------------------------------------------------------------------------
 def test_dist_mnist_tfjob_1ps_2workers_cpu(cluster):
     job = yaml.safe_load(open(os.path.join(REPO, "examples", "dist_mnist", "tf_job_mnist.yaml")))

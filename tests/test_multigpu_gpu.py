@@ -57,7 +57,9 @@ def run_job(cluster, job, timeout=300):
     cli.wait_for_job(name, polling_interval=0.2, timeout_seconds=timeout)
     ok = cli.is_job_succeeded(name)
     logs = cli.get_logs(name, master=False)
-    assert ok, "\n".join(f"--- {k}\n{v[-3000:]}" for k, v in logs.items())
+    pods = {p["metadata"]["name"]: {k: (p.get("status") or {}).get(k) for k in ("phase", "conditions", "reason")}
+            for p in cluster.store.list("pods")}
+    assert ok, f"pods: {pods}\n" + "\n".join(f"--- {k}\n{v[-3000:]}" for k, v in logs.items())
     return cli, logs
 
 

@@ -130,6 +130,7 @@ class LocalKubelet:
         self._gpu_locks = _HostGpuLocks(self.topology)
         self._pods: Dict[tuple, _PodRuntime] = {}
         self._pending_gang: Dict[tuple, Dict[str, Any]] = {}
+        self._unschedulable: Dict[tuple, tuple] = {}    # (ns, name) -> (pod, group): retried on release
         self._lock = threading.RLock()
         self._stop = threading.Event()
         self._log_dir = Path(self.opt.log_dir or tempfile.mkdtemp(prefix="tfop-logs-"))
@@ -175,6 +176,7 @@ class LocalKubelet:
         elif etype == "DELETED":
             with self._lock:
                 self._pending_gang.pop(key, None)
+                self._unschedulable.pop(key, None)
                 rt = self._pods.pop(key, None)
             if rt is not None and rt.uid == obj["metadata"].get("uid"):
                 threading.Thread(target=self._kill, args=(rt,), daemon=True).start()
@@ -239,9 +241,13 @@ class LocalKubelet:
                 want = self._gpus_wanted(pod)
                 gpus = self._claim_gpus(want) if want else []
                 if gpus is None:
+                    # stays Pending with PodScheduled=False, like a pod the scheduler cannot
+                    # place; tried again whenever a pod gives its GPUs back
+                    self._unschedulable[(c.namespace_of(pod), c.name_of(pod))] = (pod, group)
                     self._fail_unschedulable(pod, f"Insufficient {GPU_RESOURCE}: want {want}, "
                                                   f"free {len(self._free_gpus)}")
                     continue
+                self._unschedulable.pop((c.namespace_of(pod), c.name_of(pod)), None)
                 for g in gpus:
                     self._free_gpus.remove(g)
                 rt = _PodRuntime(pod)
@@ -271,6 +277,13 @@ class LocalKubelet:
                 self._gpu_locks.release(g)
 
     def _fail_unschedulable(self, pod, message: str) -> None:
+        try:
+            pod = self.store.get("pods", c.namespace_of(pod), c.name_of(pod))
+        except ApiError:
+            return
+        conds = (pod.get("status") or {}).get("conditions") or []
+        if any(x.get("reason") == "Unschedulable" and x.get("message") == message for x in conds):
+            return
         st = pod.setdefault("status", {})
         st["phase"] = c.POD_PENDING
         st["conditions"] = [{"type": "PodScheduled", "status": "False", "reason": "Unschedulable",
@@ -458,6 +471,9 @@ class LocalKubelet:
                 if g not in self._free_gpus:
                     self._free_gpus.append(g)
             rt.gpus = []
+            for key in list(self._unschedulable):
+                pod, group = self._unschedulable.pop(key)
+                self._admit([pod], group=group)      # goes back on the list if it still does not fit
         self._try_admit_gangs()
 
     def _kill(self, rt: _PodRuntime) -> None:
