@@ -159,6 +159,12 @@ def main():
                     help="use the P2P two-shot all-reduce even when NVLS multicast is available")
     ap.add_argument("--comm-blocks", type=int, default=32)
     ap.add_argument("--bucket-mb", type=int, default=16)
+    ap.add_argument("--diag-step-times", action="store_true",
+                    help="DIAGNOSTIC: also record every step's device time on every rank and report "
+                         "the spread (how much a per-step synchronisation of jittering GPUs costs)")
+    ap.add_argument("--diag-no-allreduce", action="store_true",
+                    help="DIAGNOSTIC, not a benchmark: skip the gradient all-reduce so every rank "
+                         "free-runs; shows how far apart the GPUs are on their own")
     ap.add_argument("--launch-trials", type=int, default=10,
                     help="PyTorchJobs of N real GPU replicas launched for the launch-to-Running / "
                          "launch-to-first-step p50 (0 = skip)")
@@ -191,6 +197,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+        host_pg = dist.new_group(backend="gloo")     # waits that must not occupy the GPUs
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
     torch.backends.cudnn.benchmark = True
     torch.manual_seed(1234 + rank)
@@ -206,6 +213,13 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def host_barrier():
+        # the launched replicas below run on these same GPUs: a rank waiting in an NCCL barrier
+        # would time-slice its GPU with them
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=host_pg)
 
     def max_over_ranks(ms: float) -> float:
         if world == 1:
@@ -241,6 +255,9 @@ def main():
                                    rank, world, nparam * 2 + (8 << 20),
                                    nvls_bytes=0 if args.no_nvls else nparam * 2 + (1 << 20))
             use_nvls = comm.nvls_bytes > 0
+            if args.diag_no_allreduce:
+                comm.all_reduce_nvls = lambda *a, **k: None
+                comm.all_reduce = lambda *a, **k: None
         eng = DataParallelEngine(model, comm=comm, batch_size=B, image_size=S, lr=0.1,
                                  momentum=0.9, weight_decay=1e-4, graph=not args.no_graph,
                                  overlap=not args.no_overlap, comm_blocks=args.comm_blocks,
@@ -322,12 +339,37 @@ def main():
         time.sleep(0.3)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = []
     e0.record(main_stream)
     for _ in range(args.steps):
         device_step()
+        if args.diag_step_times:
+            marks.append(torch.cuda.Event(enable_timing=True))
+            marks[-1].record(main_stream)
     e1.record(main_stream)
     barrier()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ms_mine = e0.elapsed_time(e1)
+    ms_total = max_over_ranks(ms_mine)
+    per_rank = [ms_mine / args.steps]
+    if world > 1:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, ms_mine / args.steps)
+    step_stats = None
+    if args.diag_step_times:
+        mine = [a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks)]
+        allr = [mine]
+        if world > 1:
+            allr = [None] * world
+            dist.all_gather_object(allr, mine)
+        if rank == 0:
+            import statistics as st
+            step_stats = {
+                "per_rank_mean_ms": [round(st.mean(r), 4) for r in allr],
+                "per_rank_stdev_ms": [round(st.pstdev(r), 4) for r in allr],
+                "per_rank_max_ms": [round(max(r), 4) for r in allr],
+                # what a per-step synchronisation of these free-running ranks would cost
+                "mean_of_stepwise_max_ms": round(st.mean(max(c) for c in zip(*allr)), 4),
+                "max_of_means_ms": round(max(st.mean(r) for r in allr), 4)}
     clocks = sampler.stop() if sampler else None
 
     # ---------------- end-to-end region (pinned host -> device every step, loss read back) ---
@@ -350,7 +392,7 @@ def main():
             product = _through_the_product(args, world)
         except Exception as e:  # noqa: BLE001 - the headline numbers above stand on their own
             product = {"error": f"{type(e).__name__}: {e}"[:500]}
-    barrier()
+    host_barrier()
 
     if rank == 0:
         gb = B * world
@@ -381,6 +423,12 @@ def main():
                     "last_loss": round(last_loss, 4)},
             "gpu_launches": launches_per_step * args.steps,
         }
+        if world > 1:
+            out["ms_per_step_per_rank"] = [round(x, 4) for x in per_rank]
+        if step_stats:
+            out["step_time_spread"] = step_stats
+        if args.diag_no_allreduce:
+            out["diagnostic"] = "gradient all-reduce skipped: NOT a benchmark number"
         if product:
             out.update({k: v for k, v in product.items()})
             if "launch" in product:

@@ -191,6 +191,16 @@ int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_ids_i64,
                          const void* seg_off_i64, const void* perm_i64, size_t n_uniq,
                          const void* grad, int grad_dtype, float lr, float eps, float grad_scale,
                          int max_blocks, cudaStream_t stream);
+/* The same push with duplicate ids merged on the device (hash insert, compact, sum, apply:
+ * four kernels, no sort, no host round trip, no allocation). ids as the batch names them
+ * (negative = padding). The six scratch arrays are sized by tfop_ps_dedup_workspace; before the
+ * first use fill keys with 0xFF and the rest with zero - every call leaves them in that state. */
+int tfop_ps_dedup_workspace(size_t n_ids, int dim, size_t* sizes6);
+int tfop_ps_push_adagrad_dedup(const tfop_ps_table* table, const void* ids_i64, size_t n_ids,
+                               const void* grad, int grad_dtype, float lr, float eps,
+                               float grad_scale, void* ws_keys, void* ws_slot_of, void* ws_dense,
+                               void* ws_uniq, void* ws_count, void* ws_sums, int max_blocks,
+                               cudaStream_t stream);
 
 /* ---- gradient histogram build for boosted trees (csrc/hist.cu) --------------
  * The per-worker step in front of the rabit histogram all-reduce of

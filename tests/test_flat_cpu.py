@@ -22,12 +22,15 @@ def test_flat_params_alias_and_layout():
     # writing the flat buffer changes the model
     fp.weights.zero_()
     assert all(float(p.abs().sum()) == 0.0 for p in m.parameters())
-    # buckets tile the flat range without gaps and never mix decay / no-decay slots
+    # buckets tile the flat range without gaps; the no-decay tail (complete only when backward
+    # ends) rides in the last bucket instead of costing a collective of its own
     assert fp.buckets[0].lo == 0 and fp.buckets[-1].hi == fp.total
     for a, b in zip(fp.buckets, fp.buckets[1:]):
         assert a.hi == b.lo
-    for b in fp.buckets:
-        assert len({s.decay for s in b.slots}) == 1
+    for b in fp.buckets[:-1]:
+        assert all(s.decay for s in b.slots)
+    assert any(not s.decay for s in fp.buckets[-1].slots) and fp.buckets[-1].slots[0].decay
+    assert sum(len(b.slots) for b in fp.buckets) == len(fp.slots)
     assert len(fp.buckets) >= 3
 
 

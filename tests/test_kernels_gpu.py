@@ -270,6 +270,48 @@ def test_ps_gather_and_fused_adagrad(dev, shards, dtype):
     assert torch.equal(new[~touched], full[~touched])     # untouched rows are untouched
 
 
+def test_ps_push_merges_duplicates_on_the_device_and_leaves_its_scratch_clean(dev):
+    """K5b (hash insert / compact / sum / apply) against the sort-based merge on the same data,
+    twice in a row on one scratch, padding ids skipped, then replayed from a CUDA graph (no host
+    round trip, no allocation inside)."""
+    from tf_operator_b200.ops.ps_embedding import ShardedEmbedding
+    torch.manual_seed(11)
+    rows, dim, n = 5000, 64, 8192 * 4
+    a = ShardedEmbedding.local(rows, dim, num_shards=2, device=dev, lr=0.1)
+    b = ShardedEmbedding.local(rows, dim, num_shards=2, device=dev, lr=0.1)
+    for x, y in zip(a.shards, b.shards):
+        y.copy_(x)
+    for it in range(2):
+        ids = (torch.rand(n, device=dev).pow(3.0) * (rows - 1)).long()     # hot head, like the bench
+        ids[::97] = -1                                                     # padding
+        g = torch.randn(n, dim, device=dev)
+        a.push(ids, g)
+        keep = ids >= 0
+        b.push_sorted(ids[keep], g[keep])
+        torch.cuda.synchronize()
+        for x, y in zip(a.shards + a.accums, b.shards + b.accums):
+            torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-6)
+        keys, slot_of, dense, uniq, count, sums = a._workspace(dev, n)
+        assert bool((keys == 0xFF).all()) and bool((sums == 0).all())
+        assert int(count[:4].view(torch.int32).item()) == int(torch.unique(ids[keep]).numel())
+    ids = (torch.rand(n, device=dev).pow(3.0) * (rows - 1)).long()
+    g = torch.randn(n, dim, device=dev)
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(st):
+        a.push(ids, g, stream=st)                  # warm: the scratch exists before capture
+        with torch.cuda.graph(graph, stream=st):
+            a.push(ids, g, stream=st)
+    b.push_sorted(ids, g)
+    b.push_sorted(ids, g)
+    graph.replay()
+    b.push_sorted(ids, g)
+    torch.cuda.synchronize()
+    for x, y in zip(a.shards + a.accums, b.shards + b.accums):
+        torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-6)
+
+
 def test_ps_lookup_autograd_pushes_on_backward(dev):
     from tf_operator_b200.ops.ps_embedding import ShardedEmbedding
     emb = ShardedEmbedding.local(100, 8, num_shards=2, device=dev, lr=0.5)

@@ -130,6 +130,142 @@ __global__ void __launch_bounds__(256) ps_push_adagrad_kernel(
     }
 }
 
+// ---- K5b: duplicate ids merged on the device, without a sort ---------------------------------
+// A worker's batch names the same row many times (hot ids). Adagrad is not linear in the
+// gradient, so the gradients of one id must be summed before the update. Four short kernels on
+// one stream, no host round trip, no allocation, capturable in a CUDA graph:
+//   1 insert  : every position puts its id into an open-addressing table (64-bit CAS, linear
+//               probing) and remembers the slot it landed in;
+//   2 compact : every occupied slot takes the next dense index, publishes (id -> index) and
+//               empties itself again (the table is clean for the next call);
+//   3 sum     : every position adds its gradient row into row `index` of an fp32 scratch
+//               (vector red.add, duplicates meet here);
+//   4 apply   : every dense index applies Adagrad on the owning shard over NVLink and zeroes
+//               its scratch row again.
+// The scratch (keys / slot_of / dense / uniq / count / sums) is the caller's, sized by
+// tfop_ps_dedup_workspace, and must be zero-filled except keys (all ones) before first use.
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+__device__ __forceinline__ unsigned hash_id(unsigned long long id) {
+    id ^= id >> 33;
+    id *= 0xff51afd7ed558ccdull;
+    id ^= id >> 33;
+    return (unsigned)id;
+}
+
+__global__ void __launch_bounds__(256) ps_dedup_insert_kernel(
+    const long long* __restrict__ ids, size_t n_ids, unsigned long long* __restrict__ keys,
+    unsigned cap_mask, int* __restrict__ slot_of, int* __restrict__ count) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *count = 0;          // kernel 2 counts from zero
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n_ids; k += stride) {
+        const long long id = ids[k];
+        int where = -1;
+        if (id >= 0) {
+            unsigned slot = hash_id((unsigned long long)id) & cap_mask;
+            for (unsigned probe = 0; probe <= cap_mask; ++probe) {
+                const unsigned long long seen =
+                    atomicCAS(keys + slot, kEmptyKey, (unsigned long long)id);
+                if (seen == kEmptyKey || seen == (unsigned long long)id) {
+                    where = (int)slot;
+                    break;
+                }
+                slot = (slot + 1) & cap_mask;
+            }
+        }
+        slot_of[k] = where;
+    }
+}
+
+__global__ void __launch_bounds__(256) ps_dedup_compact_kernel(
+    unsigned long long* __restrict__ keys, unsigned cap, int* __restrict__ dense,
+    long long* __restrict__ uniq, int* __restrict__ count) {
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned s = blockIdx.x * blockDim.x + threadIdx.x; s < cap; s += stride) {
+        const unsigned long long k = keys[s];
+        const bool used = k != kEmptyKey;
+        // one atomic per warp: lanes with an occupied slot take consecutive indices
+        const unsigned m = __ballot_sync(0xffffffffu, used);
+        int base = 0;
+        const int lane = threadIdx.x & 31;
+        if (m != 0u) {
+            const int leader = __ffs(m) - 1;
+            if (lane == leader) base = atomicAdd(count, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+        }
+        if (used) {
+            const int idx = base + __popc(m & ((1u << lane) - 1u));
+            dense[s] = idx;
+            uniq[idx] = (long long)k;
+            keys[s] = kEmptyKey;
+        }
+    }
+}
+
+template <bool GRAD_BF16>
+__global__ void __launch_bounds__(256) ps_dedup_sum_kernel(
+    const int* __restrict__ slot_of, const int* __restrict__ dense, size_t n_ids, int dim,
+    const void* __restrict__ grad, float* __restrict__ sums) {
+    const int chunks = dim >> 2;
+    const size_t total = n_ids * (size_t)chunks;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const size_t k = i / chunks;
+        const int c = (int)(i % chunks);
+        const int slot = slot_of[k];
+        if (slot < 0) continue;
+        const size_t src = k * dim + (size_t)c * 4;
+        float4 g;
+        if (GRAD_BF16) {
+            const uint2 raw = *reinterpret_cast<const uint2*>((const __nv_bfloat16*)grad + src);
+            const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+            const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+            g = make_float4(a.x, a.y, b.x, b.y);
+        } else {
+            g = *reinterpret_cast<const float4*>((const float*)grad + src);
+        }
+        float* dst = sums + (size_t)dense[slot] * dim + (size_t)c * 4;
+        asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst),
+                     "f"(g.x), "f"(g.y), "f"(g.z), "f"(g.w)
+                     : "memory");
+    }
+}
+
+__global__ void __launch_bounds__(256) ps_dedup_apply_kernel(
+    const tfop_ps_table t, const long long* __restrict__ uniq, const int* __restrict__ count,
+    float* __restrict__ sums, float lr, float eps, float grad_scale) {
+    const int chunks = t.dim >> 2;
+    const size_t total = (size_t)(*count) * (size_t)chunks;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const size_t u = i / chunks;
+        const int c = (int)(i % chunks);
+        float4* sp = reinterpret_cast<float4*>(sums + u * t.dim + (size_t)c * 4);
+        float4 g = *sp;
+        *sp = make_float4(0.f, 0.f, 0.f, 0.f);                    // clean for the next call
+        const long long id = uniq[u];
+        const int shard = (int)(id % t.num_shards);
+        const long long row = id / t.num_shards;
+        if (row >= t.rows_per_shard) continue;
+        g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
+        const size_t off = (size_t)row * t.dim + (size_t)c * 4;
+        const float4 sq = make_float4(g.x * g.x, g.y * g.y, g.z * g.z, g.w * g.w);
+        const float4 old = atom_add_f4_sys(t.accum[shard] + off, sq);
+        float4 d;
+        d.x = -lr * g.x / (sqrtf(old.x + sq.x) + eps);
+        d.y = -lr * g.y / (sqrtf(old.y + sq.y) + eps);
+        d.z = -lr * g.z / (sqrtf(old.z + sq.z) + eps);
+        d.w = -lr * g.w / (sqrtf(old.w + sq.w) + eps);
+        red_add_f4_sys(t.weight[shard] + off, d);
+    }
+}
+
+size_t dedup_capacity(size_t n_ids) {
+    size_t cap = 1024;
+    while (cap < 2 * n_ids) cap <<= 1;
+    return cap;
+}
+
 int grid_for(size_t total, int max_blocks) {
     size_t b = (total + 255) / 256;
     size_t cap = max_blocks > 0 ? (size_t)max_blocks : (size_t)148 * 8;
@@ -184,6 +320,57 @@ TFOP_API int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_i
         ps_push_adagrad_kernel<false><<<grid, 256, 0, stream>>>(
             *table, (const long long*)uniq_ids_i64, (const long long*)seg_off_i64,
             (const long long*)perm_i64, n_uniq, grad, lr, eps, grad_scale);
+    TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Byte sizes of the six scratch arrays of tfop_ps_push_adagrad_dedup for up to n_ids positions
+// of a table of width dim: keys (fill with 0xFF), slot_of, dense, uniq, count, sums (zero-fill).
+TFOP_API int tfop_ps_dedup_workspace(size_t n_ids, int dim, size_t* sizes6) {
+    TFOP_REQUIRE(sizes6 != nullptr && dim >= 4 && dim % 4 == 0, "bad arguments");
+    const size_t cap = dedup_capacity(n_ids);
+    sizes6[0] = cap * sizeof(unsigned long long);
+    sizes6[1] = n_ids * sizeof(int);
+    sizes6[2] = cap * sizeof(int);
+    sizes6[3] = n_ids * sizeof(long long);
+    sizes6[4] = 256;
+    sizes6[5] = n_ids * (size_t)dim * sizeof(float);
+    return 0;
+}
+
+// The push with the duplicate merge on the device (K5b): ids[n_ids] int64 as the batch names
+// them (negative = padding), grad[n_ids, dim] fp32 or bf16. Allocates nothing, never blocks the
+// host; the scratch comes back clean (same state as before the call).
+TFOP_API int tfop_ps_push_adagrad_dedup(const tfop_ps_table* table, const void* ids_i64,
+                                        size_t n_ids, const void* grad, int grad_dtype, float lr,
+                                        float eps, float grad_scale, void* ws_keys,
+                                        void* ws_slot_of, void* ws_dense, void* ws_uniq,
+                                        void* ws_count, void* ws_sums, int max_blocks,
+                                        cudaStream_t stream) {
+    if (check_table(table) != 0) return -1;
+    TFOP_REQUIRE(grad_dtype == TFOP_F32 || grad_dtype == TFOP_BF16, "bad grad dtype");
+    TFOP_REQUIRE(ws_keys && ws_slot_of && ws_dense && ws_uniq && ws_count && ws_sums,
+                 "null scratch");
+    TFOP_REQUIRE(n_ids < ((size_t)1 << 30), "too many ids for one push");
+    if (n_ids == 0) return 0;
+    const size_t cap = dedup_capacity(n_ids);
+    const int chunks = table->dim / 4;
+    ps_dedup_insert_kernel<<<grid_for(n_ids, max_blocks), 256, 0, stream>>>(
+        (const long long*)ids_i64, n_ids, (unsigned long long*)ws_keys, (unsigned)(cap - 1),
+        (int*)ws_slot_of, (int*)ws_count);
+    ps_dedup_compact_kernel<<<grid_for(cap, max_blocks), 256, 0, stream>>>(
+        (unsigned long long*)ws_keys, (unsigned)cap, (int*)ws_dense, (long long*)ws_uniq,
+        (int*)ws_count);
+    const int grid = grid_for(n_ids * (size_t)chunks, max_blocks);
+    if (grad_dtype == TFOP_BF16)
+        ps_dedup_sum_kernel<true><<<grid, 256, 0, stream>>>(
+            (const int*)ws_slot_of, (const int*)ws_dense, n_ids, table->dim, grad, (float*)ws_sums);
+    else
+        ps_dedup_sum_kernel<false><<<grid, 256, 0, stream>>>(
+            (const int*)ws_slot_of, (const int*)ws_dense, n_ids, table->dim, grad, (float*)ws_sums);
+    ps_dedup_apply_kernel<<<grid, 256, 0, stream>>>(*table, (const long long*)ws_uniq,
+                                                    (const int*)ws_count, (float*)ws_sums, lr,
+                                                    eps, grad_scale);
     TFOP_CUDA(cudaGetLastError());
     return 0;
 }

@@ -132,6 +132,10 @@ _SIGS = {
     "tfop_ps_gather": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
                                      c_int, c_float, c_float, c_float, c_int, c_void_p]),
+    "tfop_ps_dedup_workspace": (c_int, [c_size_t, c_int, c_void_p]),
+    "tfop_ps_push_adagrad_dedup": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_float,
+                                           c_float, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_int, c_void_p]),
     "tfop_gemm_bf16_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                   c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
 }

@@ -33,6 +33,7 @@ class ShardedEmbedding:
         self.initial_accumulator = initial_accumulator
         self._keepalive = keepalive
         self.max_blocks = 0
+        self._dedup_ws = {}          # (device index, positions) -> scratch of the device-side merge
 
     @property
     def num_rows(self) -> int:
@@ -87,8 +88,34 @@ class ShardedEmbedding:
             _lib.dtype_tag(out_dtype), self.max_blocks, _lib.stream_handle(stream)), "ps_gather")
         return out
 
+    def _workspace(self, device, n: int):
+        key = (device.index, n)
+        ws = self._dedup_ws.get(key)
+        if ws is None:
+            sizes = (C.c_size_t * 6)()
+            _lib.check(_lib.load().tfop_ps_dedup_workspace(n, self.dim, sizes))
+            ws = [torch.zeros(int(b), dtype=torch.uint8, device=device) for b in sizes]
+            ws[0].fill_(0xFF)                   # empty key = all ones
+            self._dedup_ws[key] = ws
+        return ws
+
     def push(self, ids: torch.Tensor, grad: torch.Tensor, grad_scale: float = 1.0, stream=None) -> None:
-        """Segment-sum duplicates and apply Adagrad on the owning shards."""
+        """Sum the gradients of duplicate ids and apply Adagrad on the owning shards: four kernels
+        of csrc/ps.cu (K5b: hash insert, compact, sum, apply), no sort, no host round trip; the
+        scratch is allocated once per batch shape."""
+        ids = ids.contiguous().view(-1).to(torch.int64)
+        grad = grad.contiguous().view(ids.numel(), self.dim)
+        ws = self._workspace(ids.device, ids.numel())
+        _lib.check(_lib.load().tfop_ps_push_adagrad_dedup(
+            C.byref(self.table), ids.data_ptr(), ids.numel(), grad.data_ptr(),
+            _lib.dtype_tag(grad.dtype), float(self.lr), float(self.eps), float(grad_scale),
+            *[w.data_ptr() for w in ws], self.max_blocks, _lib.stream_handle(stream)),
+            "ps_push_adagrad_dedup")
+        _lib.LAUNCHES["ps_push_adagrad_dedup"] += 3       # four kernels behind the one entry point
+
+    def push_sorted(self, ids: torch.Tensor, grad: torch.Tensor, grad_scale: float = 1.0, stream=None) -> None:
+        """The same update with the duplicate merge done by a library sort (torch.sort +
+        unique_consecutive + cumsum, then K5): the comparator of benchmarks/ps_bench.py."""
         ids = ids.contiguous().view(-1).to(torch.int64)
         grad = grad.contiguous().view(ids.numel(), self.dim)
         sorted_ids, perm = torch.sort(ids)

@@ -99,13 +99,15 @@ class FlatParams:
                 mview.copy_(src.float())
                 view.copy_(src.to(weight_dtype))
                 p.data = view
-        # buckets: contiguous ranges of the decay region + one for the no-decay tail
+        # buckets: contiguous ranges, cut every bucket_bytes over the decay region. The no-decay
+        # tail (norm scales / biases of EVERY layer, a few hundred KB) rides in the last decay
+        # bucket: both become complete only when backward reaches the first layer, and one
+        # latency-bound collective at the end of the step is cheaper than two.
         self.buckets: List[Bucket] = []
         cur = None
         limit = max(1, bucket_bytes // 2)
         for s in self.slots:
-            if cur is None or (s.decay and cur.hi - cur.lo >= limit) or \
-                    (not s.decay and cur.slots and cur.slots[0].decay):
+            if cur is None or (s.decay and cur.hi - cur.lo >= limit):
                 cur = Bucket(s.offset, s.offset)
                 self.buckets.append(cur)
             cur.slots.append(s)
