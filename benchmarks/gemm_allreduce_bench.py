@@ -17,6 +17,7 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
+from tf_operator_b200.ops import _lib  # noqa: E402
 from tf_operator_b200.ops.gemm import gemm_tn  # noqa: E402
 from tf_operator_b200.runtime.symm import TWO_SHOT, SymmetricComm  # noqa: E402
 
@@ -105,6 +106,30 @@ def main():
             row["fused_nvls_us"] = round(timed(lambda: comm.gemm_all_reduce_nvls(
                 a, b, ws_off=ws_off, scale=1.0 / world)), 1)
             say(f"  fused nvls correct={goodn} err={errn:.4f} {row['fused_nvls_us']} us")
+            # the same kernel at both tile widths, and the first-generation kernel (one CTA per
+            # tile, 3 stages); the counters' layout follows the tile count: zero in between
+            lib = _lib.load()
+            for name, tile_n, legacy in (("fused_nvls_tile128_us", 128, 0), ("fused_nvls_tile256_us", 256, 0),
+                                         ("fused_nvls_first_generation_us", 0, 1)):
+                lib.tfop_gemm_allreduce_set_tile_n(tile_n)
+                lib.tfop_gemm_allreduce_set_legacy(legacy)
+                torch.cuda.synchronize()
+                dist.barrier()
+                comm.view(ws_off, out_off - ws_off, torch.uint8).zero_()
+                torch.cuda.synchronize()
+                dist.barrier()
+                row[name] = round(timed(lambda: comm.gemm_all_reduce_nvls(
+                    a, b, ws_off=ws_off, scale=1.0 / world)), 1)
+                ok &= not comm.check_error()
+            lib.tfop_gemm_allreduce_set_tile_n(0)
+            lib.tfop_gemm_allreduce_set_legacy(0)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.view(ws_off, out_off - ws_off, torch.uint8).zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            say(f"  tile128 {row['fused_nvls_tile128_us']} tile256 {row['fused_nvls_tile256_us']} "
+                f"first-generation {row['fused_nvls_first_generation_us']} us")
         # unfused, all ours: tcgen05 GEMM into symmetric memory, then in-place fused all-reduce
         sym_out = comm.view(out_off, m * n, torch.bfloat16).view(m, n)
 

@@ -20,12 +20,10 @@ import torch.nn.functional as F
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 
-from tf_operator_b200.launcher.rendezvous import RendezvousClient  # noqa: E402
 from tf_operator_b200.models.wide_deep import WideAndDeep  # noqa: E402
 from tf_operator_b200.ops.ps_embedding import ShardedEmbedding  # noqa: E402
 from tf_operator_b200.parallel.engine import FlatDataParallel  # noqa: E402
-from tf_operator_b200.runtime.env import ReplicaContext  # noqa: E402
-from tf_operator_b200.runtime.symm import SymmetricComm  # noqa: E402
+from tf_operator_b200.runtime.env import ReplicaContext, rendezvous_comm  # noqa: E402
 
 
 def main():
@@ -57,11 +55,13 @@ def main():
         is_ps = ctx.task_type == "ps"
         rank = ctx.task_index if is_ps else n_ps + ctx.task_index
         world = n_ps + n_workers
-        rdv = RendezvousClient(ctx.raw["TFOP_RENDEZVOUS"])
-        prefix = f"{ctx.namespace}/{ctx.job_name}"
+        # peer handles go through the launcher's rendezvous store under <ns>/<job>/<job uid>/...
+        # (a re-created job of the same name never sees its predecessor's handles) and in the
+        # scope's current generation (a restarted replica re-forms the group)
+        addr, uds = ctx.raw["TFOP_RENDEZVOUS"], ctx.raw.get("TFOP_RENDEZVOUS_UDS", "")
         nbytes = wide_off + wide_bytes if is_ps else (1 << 20)
-        comm = SymmetricComm.create(rank, world, nbytes,
-                                    lambda b: rdv.all_gather(prefix + "/ps-ipc", rank, world, b))
+        comm = rendezvous_comm(addr, uds, ctx.rendezvous_scope("ps"), rank, world, nbytes)
+        rdv, prefix = comm._rdv
         if is_ps:
             ShardedEmbedding.init_local_shard(comm, rows_per_shard, args.dim, 0, seed=ctx.task_index)
             ShardedEmbedding.init_local_shard(comm, rows_per_shard, 4, wide_off, seed=100 + ctx.task_index)
@@ -79,10 +79,8 @@ def main():
         rank_w = ctx.task_index
         comm_w = None
         if n_workers > 1:
-            comm_w = SymmetricComm.create(
-                rank_w, n_workers, 64 << 20,
-                lambda b: rdv.all_gather(prefix + "/worker-ipc", rank_w, n_workers, b))
-            rdv.barrier(prefix + "/workers-ready", n_workers)
+            comm_w = rendezvous_comm(addr, uds, ctx.rendezvous_scope("workers"), rank_w, n_workers,
+                                     64 << 20)
 
     torch.manual_seed(1234)
     model = WideAndDeep(deep, wide, num_fields=args.fields, embed_dim=args.dim).to(dev).to(torch.bfloat16)
@@ -118,7 +116,10 @@ def main():
            "kernel_launches_per_step": dp.kernel_launches_per_step}
     print(json.dumps(out), flush=True)
     if not local:
-        rdv.barrier(prefix + "/done", n_workers)
+        torch.cuda.synchronize()
+        rdv.barrier(prefix + "/done", n_workers)      # nobody leaves while a peer still pushes
+        if comm_w is not None:
+            comm_w.close()
     return 0
 
 

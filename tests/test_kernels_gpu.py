@@ -273,7 +273,8 @@ def test_ps_gather_and_fused_adagrad(dev, shards, dtype):
 def test_ps_push_merges_duplicates_on_the_device_and_leaves_its_scratch_clean(dev):
     """K5b (hash insert / compact / sum / apply) against the sort-based merge on the same data,
     twice in a row on one scratch, padding ids skipped, then replayed from a CUDA graph (no host
-    round trip, no allocation inside)."""
+    round trip, no allocation inside). Tolerance: hot rows sum hundreds of fp32 gradients in a
+    different order in the two paths."""
     from tf_operator_b200.ops.ps_embedding import ShardedEmbedding
     torch.manual_seed(11)
     rows, dim, n = 5000, 64, 8192 * 4
@@ -290,7 +291,7 @@ def test_ps_push_merges_duplicates_on_the_device_and_leaves_its_scratch_clean(de
         b.push_sorted(ids[keep], g[keep])
         torch.cuda.synchronize()
         for x, y in zip(a.shards + a.accums, b.shards + b.accums):
-            torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-6)
+            torch.testing.assert_close(x, y, rtol=1e-4, atol=1e-5)
         keys, slot_of, dense, uniq, count, sums = a._workspace(dev, n)
         assert bool((keys == 0xFF).all()) and bool((sums == 0).all())
         assert int(count[:4].view(torch.int32).item()) == int(torch.unique(ids[keep]).numel())
@@ -309,7 +310,7 @@ def test_ps_push_merges_duplicates_on_the_device_and_leaves_its_scratch_clean(de
     b.push_sorted(ids, g)
     torch.cuda.synchronize()
     for x, y in zip(a.shards + a.accums, b.shards + b.accums):
-        torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(x, y, rtol=1e-4, atol=1e-5)
 
 
 def test_ps_lookup_autograd_pushes_on_backward(dev):

@@ -82,7 +82,8 @@ def test_collective_kernels_on_real_peer_mappings(cluster, tmp_path):
             "gemm_allreduce_p2p"} <= names
     if res[0]["nvls"]:
         assert {"nvls_outofplace_bfloat16", "nvls_inplace_bf16", "nvls_inplace_bf16_second_call",
-                "gemm_allreduce_nvls"} <= names
+                "gemm_allreduce_nvls", "gemm_allreduce_nvls_tile128_call2",
+                "gemm_allreduce_nvls_tile256_call2", "gemm_allreduce_nvls_wgrad_layout"} <= names
     for r in res:
         bad = {k: v for k, v in r["checks"].items() if not v["ok"] or v["error_word_after"]}
         assert not bad, (r["rank"], bad)
@@ -187,3 +188,38 @@ def test_killed_replica_reforms_the_gang_and_training_resumes(cluster, tmp_path)
     assert out["world"] == WORLD and out["final_loss"] == out["final_loss"]
     master_log = logs["mg-restart-master-0"]
     assert "resume_step 20" in master_log
+
+
+def test_ps_worker_tfjob_trains_on_a_table_sharded_over_the_ps_replicas(cluster):
+    """BASELINE.json config 4 in small: a TFJob with PS and Worker replicas (TF_CONFIG roles as in
+    examples/v1/dist-mnist/dist_mnist.py:102-146). Workers pull rows out of the PS replicas' HBM
+    and push Adagrad updates into it over NVLink (K4 / K5b); the job succeeds when all workers
+    finish (successPolicy AllWorkers) and the still-running PS replicas are cleaned up."""
+    import yaml
+    from tf_operator_b200.sdk import TFJobClient
+    n_ps = 1 if WORLD < 4 else 2
+    job = yaml.safe_load(open(os.path.join(REPO, "examples", "wide_deep_ps", "tfjob.yaml")))
+    specs = job["spec"]["tfReplicaSpecs"]
+    specs["PS"]["replicas"], specs["Worker"]["replicas"] = n_ps, WORLD - n_ps
+    for rt in specs:
+        ctr = specs[rt]["template"]["spec"]["containers"][0]
+        ctr["command"] = list(ctr["command"]) + ["--rows=200000", "--batch-size=2048", "--steps=10",
+                                                 "--warmup=2"]
+    cli = TFJobClient(cluster=cluster)
+    cli.create(job)
+    name = job["metadata"]["name"]
+    cli.wait_for_job(name, polling_interval=0.2, timeout_seconds=300)
+    logs = cli.get_logs(name, master=False)
+    assert cli.is_job_succeeded(name), "\n".join(f"--- {k}\n{v[-2000:]}" for k, v in logs.items())
+    rows = [json.loads(ln) for text in logs.values() for ln in text.splitlines()
+            if ln.startswith('{"role": "worker"')]
+    assert len(rows) == WORLD - n_ps
+    assert all(r["loss"] == r["loss"] and r["ps"] == n_ps and r["ids_per_step"] == 2048 * 26 for r in rows)
+    # cleanPodPolicy Running: the PS replicas (server.join()) are gone once the job is done
+    deadline = time.time() + 20
+    while time.time() < deadline and any(
+            p["metadata"]["name"].startswith(f"{name}-ps-") and
+            (p.get("status") or {}).get("phase") == "Running" for p in cluster.store.list("pods")):
+        time.sleep(0.1)
+    assert not any(p["metadata"]["name"].startswith(f"{name}-ps-") and
+                   (p.get("status") or {}).get("phase") == "Running" for p in cluster.store.list("pods"))

@@ -118,9 +118,31 @@ def main():
     got = comm.gemm_all_reduce(a, b, ws_off=0, out_off=out_off)
     record("gemm_allreduce_p2p", got, want, 2e-2, 2e-2)
     if comm.nvls_bytes:
+        from tf_operator_b200.ops import _lib
+        lib = _lib.load()
+        # the cta_group::2 pipeline with reducer warps, both tile widths, twice on one set of
+        # counters (generation 1 and 2), then the weight-gradient operand layout (both MN-major),
+        # then the first-generation kernel
+        for tile_n in (128, 256):
+            lib.tfop_gemm_allreduce_set_tile_n(tile_n)
+            fresh_workspace()
+            for call in (1, 2):
+                got = comm.gemm_all_reduce_nvls(a, b, ws_off=0, out_off=0)
+                record(f"gemm_allreduce_nvls_tile{tile_n}_call{call}", got, want, 2e-2, 2e-2)
+                torch.cuda.synchronize()
+                comm._exit_barrier()
+        lib.tfop_gemm_allreduce_set_tile_n(0)
+        fresh_workspace()
+        got = comm.gemm_all_reduce_nvls(a.t().contiguous(), b.t().contiguous(), ws_off=0, out_off=0,
+                                        a_mn=True, b_mn=True)
+        record("gemm_allreduce_nvls_wgrad_layout", got, want, 2e-2, 2e-2)
+        torch.cuda.synchronize()
+        comm._exit_barrier()
+        lib.tfop_gemm_allreduce_set_legacy(1)
         fresh_workspace()
         got = comm.gemm_all_reduce_nvls(a, b, ws_off=0, out_off=0)
         record("gemm_allreduce_nvls", got, want, 2e-2, 2e-2)
+        lib.tfop_gemm_allreduce_set_legacy(0)
     res["error_word"] = comm.check_error()
     with open(os.path.join(out_dir, f"rank{R}.json"), "w") as f:
         json.dump(res, f)

@@ -33,6 +33,9 @@
 int tfop_gemm_make_tensor_map(CUtensorMap* map, const void* base, int rows, int K, int ld,
                               int box_rows);
 int tfop_gemm_num_sms(int* out);
+int tfop_gemm_launch_fused(const void* A, const void* B, void* C_local, int M, int N, int K,
+                           int lda, int ldb, int ldo, int a_mn, int b_mn, int tile_n,
+                           const tfop_gemm::GemmFuse* fz, int max_ctas, cudaStream_t stream);
 
 namespace {
 
@@ -494,26 +497,82 @@ TFOP_API int tfop_gemm_allreduce_bf16_tn(tfop_comm* c, const void* A, const void
     return 0;
 }
 
-// NVLS flavour of tfop_gemm_allreduce_bf16_tn: the result region is at out_off of the
-// communicator's multicast-bound buffer (tfop_nvls_bind), partial tiles never leave their GPU and
-// the NVSwitch does the summation (multimem.ld_reduce) and the broadcast (multimem.st).
-// ws_off: (tiles_per_owner + 2) * 4 bytes of zeroed counters in the IPC symmetric buffer.
-// N and ldo must be multiples of 8.
-TFOP_API int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const void* B, int M,
-                                              int N, int K, int lda, int ldb, int ldo, float scale,
-                                              size_t ws_off, size_t out_off, int max_ctas,
-                                              cudaStream_t stream) {
+// Test / benchmark hooks of the NVLS flavour: tile width (0 = heuristic, 128, 256) and 1 to run
+// the first-generation kernel (one CTA per tile, 3-stage pipeline) for comparison.
+static int g_nvls_tile_n = 0;
+static int g_nvls_legacy = 0;
+TFOP_API int tfop_gemm_allreduce_set_tile_n(int tile_n) {
+    TFOP_REQUIRE(tile_n == 0 || tile_n == 128 || tile_n == 256, "tile_n must be 0, 128 or 256");
+    g_nvls_tile_n = tile_n;
+    return 0;
+}
+TFOP_API int tfop_gemm_allreduce_set_legacy(int on) {
+    g_nvls_legacy = on;
+    return 0;
+}
+
+// NVLS flavour: out[M,N] (bf16, at out_off of the communicator's multicast-bound buffer
+// (tfop_nvls_bind), row pitch ldo, in EVERY rank's copy) = scale * sum over ranks of
+// op(A_r) * op(B_r)^T with a_mn / b_mn as in tfop_gemm_bf16 ((1,1) = the weight gradient
+// dY^T X straight from the stored activations). One kernel: the cta_group::2 GEMM pipeline of
+// gemm_tcgen05.cu stores each partial tile into the local copy, tells the tile's owner, and
+// reducer warps in the same CTAs let the NVSwitch sum (multimem.ld_reduce) and broadcast
+// (multimem.st) the tiles as they complete. Partial tiles never cross NVLink as such.
+// ws_off: (tiles + 2) * 4 bytes of zeroed counters in the IPC symmetric buffer, tiles counted
+// at 128 x 128 (tfop_gemm_allreduce_nvls_workspace_bytes); tied to one (M, N, world).
+// N and ldo must be multiples of 8. All ranks call with the same arguments.
+TFOP_API size_t tfop_gemm_allreduce_nvls_workspace_bytes(int M, int N, int world) {
+    const int tiles = (((M + BLOCK_M - 1) / BLOCK_M) + 1) / 2 * 2 * ((N + 127) / 128);
+    return (((size_t)(tiles + world - 1) / world + 2) * 4 + 255) & ~(size_t)255;
+}
+
+TFOP_API int tfop_gemm_allreduce_nvls_bf16(tfop_comm* c, const void* A, const void* B, int M,
+                                           int N, int K, int lda, int ldb, int ldo, int a_mn,
+                                           int b_mn, float scale, size_t ws_off, size_t out_off,
+                                           int max_ctas, cudaStream_t stream) {
     TFOP_REQUIRE(c != nullptr && !c->emulated, "needs a real communicator");
     TFOP_REQUIRE(c->mc_ptr != nullptr, "NVLS is not set up on this communicator");
     TFOP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "lda/ldb must be multiples of 8 elements (TMA)");
     TFOP_REQUIRE(N % 8 == 0 && ldo % 8 == 0 && (out_off & 15) == 0,
                  "NVLS mode needs N, ldo multiples of 8 and a 16-byte aligned out_off");
     TFOP_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
+    TFOP_REQUIRE(out_off + ((size_t)(M - 1) * ldo + N) * 2 <= c->mc_bytes,
+                 "output region does not fit the NVLS buffer");
+    const int m_blocks = (M + BLOCK_M - 1) / BLOCK_M;
+    const bool legacy = g_nvls_legacy || (m_blocks < 2 && !a_mn && !b_mn);
+    int sms = 0;
+    if (tfop_gemm_num_sms(&sms) != 0) return -1;
+    if (!legacy) {
+        // wide tiles when they fill the machine; narrower ones otherwise, so that the first
+        // wave's tiles travel while the second wave multiplies
+        int tile_n = g_nvls_tile_n;
+        if (tile_n == 0) {
+            const long pairs256 = (long)((m_blocks + 1) / 2) * ((N + 255) / 256);
+            tile_n = (N >= 256 && pairs256 >= sms / 2) ? 256 : 128;
+        }
+        // tiles are owned by production sequence number: 2 per scheduling unit (CTA pair)
+        const int tiles = (m_blocks + 1) / 2 * 2 * ((N + tile_n - 1) / tile_n);
+        const int tpo = (tiles + c->world - 1) / c->world;
+        TFOP_REQUIRE((ws_off & 15) == 0 && ws_off + ((size_t)tpo + 2) * 4 <= c->data_bytes,
+                     "counter workspace does not fit the symmetric buffer");
+        tfop_gemm::GemmFuse fz;
+        memset(&fz, 0, sizeof(fz));
+        for (int p = 0; p < c->world; ++p) fz.arrived[p] = (uint32_t*)((char*)c->data[p] + ws_off);
+        fz.mc_out = (char*)c->mc_ptr + out_off;
+        fz.err = c->sig[c->rank] + TFOP_SIG_WORDS;
+        fz.timeout = g_spin_timeout;
+        fz.rank = c->rank;
+        fz.world = c->world;
+        fz.tiles_per_owner = tpo;
+        fz.ldo = ldo;
+        fz.scale = scale;
+        return tfop_gemm_launch_fused(A, B, (char*)c->mc_uc_ptr + out_off, M, N, K, lda, ldb, ldo,
+                                      a_mn, b_mn, tile_n, &fz, max_ctas, stream);
+    }
+    TFOP_REQUIRE(!a_mn && !b_mn, "the first-generation kernel takes K-major operands only");
     const int tpo = tiles_per_owner(M, N, c->world);
     TFOP_REQUIRE((ws_off & 15) == 0 && ws_off + ((size_t)tpo + 2) * 4 <= c->data_bytes,
                  "counter workspace does not fit the symmetric buffer");
-    TFOP_REQUIRE(out_off + ((size_t)(M - 1) * ldo + N) * 2 <= c->mc_bytes,
-                 "output region does not fit the NVLS buffer");
     GarArgs a;
     memset(&a, 0, sizeof(a));
     for (int p = 0; p < c->world; ++p) a.data[p] = (char*)c->data[p];
@@ -534,14 +593,21 @@ TFOP_API int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const
         TFOP_CUDA(cudaFuncSetAttribute(gemm_allreduce_nvls_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kGarSmemBytes));
     }
-    int sms = 0;
-    if (tfop_gemm_num_sms(&sms) != 0) return -1;
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BN - 1) / BN);
     int grid = tiles < sms ? tiles : sms;
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
     gemm_allreduce_nvls_kernel<<<grid, kGarThreads, kGarSmemBytes, stream>>>(ma, mb, a);
     TFOP_CUDA(cudaGetLastError());
     return 0;
+}
+
+// K-major operands (F.linear layout): the entry point of round 1, kept.
+TFOP_API int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const void* B, int M,
+                                              int N, int K, int lda, int ldb, int ldo, float scale,
+                                              size_t ws_off, size_t out_off, int max_ctas,
+                                              cudaStream_t stream) {
+    return tfop_gemm_allreduce_nvls_bf16(c, A, B, M, N, K, lda, ldb, ldo, 0, 0, scale, ws_off,
+                                         out_off, max_ctas, stream);
 }
 
 // Single-GPU emulation for tests: all `world` (<= 4) ranks of an emulated communicator group

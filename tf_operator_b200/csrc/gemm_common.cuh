@@ -277,4 +277,45 @@ __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
                  : "memory");
 }
 
+// ---- GEMM -> all-reduce in one kernel (NVLS flavour, see gemm_allreduce.cu) -----------------
+// The GEMM kernel run with kFuse writes its bf16 partial tiles with TMA stores into the LOCAL
+// copy of the multicast-bound output region, tells the tile's owner rank, and four extra warps
+// per CTA reduce this rank's owned tiles inside the NVSwitch as they become complete on all
+// ranks. arrived[r]: rank r's counter block in its symmetric buffer as mapped here:
+//   arrived[tiles_per_owner] | delivered | generation      (monotone, never reset)
+constexpr int kFuseThreads = 384;   // 4 control + 4 epilogue + 4 reducer warps
+constexpr int kFuseRedWarp0 = 8;
+struct GemmFuse {
+    uint32_t* arrived[8];
+    char* mc_out;            // multicast view of the output region, row pitch ldo elements
+    uint32_t* err;
+    long long timeout;
+    int rank, world, tiles_per_owner, ldo;
+    float scale;
+};
+
+__device__ __forceinline__ void bulk_wait_all() {      // writes complete, not only reads
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ void fuse_red_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 fuse_mm_ld_reduce_bf16x8(const void* mc) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(mc)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void fuse_mm_st_16(void* mc, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc),
+                 "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                 "f"(__uint_as_float(v.w))
+                 : "memory");
+}
+__device__ __forceinline__ void fuse_reducer_bar() {   // named barrier 2: the 128 reducer threads
+    asm volatile("bar.sync 2, 128;" ::: "memory");
+}
+
 }  // namespace tfop_gemm

@@ -90,13 +90,22 @@ __device__ __forceinline__ void stage_bias(float* sbias, const void* bias, int b
 // pack kernels to be resident NEXT TO a GEMM CTA - with 241 registers the gradient all-reduce of
 // a data-parallel step could only run between GEMMs (+1.1 ms per BERT-large step at 2 and at 8
 // GPUs alike).
-template <int BN, bool kTmaStore, int kCluster>
+//
+// kFuse (gemm_allreduce.cu, NVLS flavour): C is this rank's copy of a multicast-bound region. An
+// epilogue warp that has stored its 32 rows of a tile waits for the stores to land, then bumps
+// the tile's arrival counter on the OWNER rank (tile id % world) with a release RED over NVLink.
+// Warps 8-11 take this rank's owned tiles as they become complete on every rank: the NVSwitch
+// sums the ranks' copies (multimem.ld_reduce), the result goes to every rank (multimem.st), and
+// each rank's `delivered` counter is bumped. The kernel ends when this rank's whole C is in.
+template <int BN, bool kTmaStore, int kCluster, bool kFuse = false>
 __global__ void __maxnreg__(136)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_c, void* __restrict__ C, const void* __restrict__ bias, int bias_dtype, int M, int N,
-               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn, int group_m, int splits) {
+               int K, int ldc, int out_dtype, int epi, int a_mn, int b_mn, int group_m, int splits,
+               const GemmFuse fz) {
     using cfg = Cfg<BN, kCluster>;
     constexpr bool kPair = kCluster == 2;
+    static_assert(!kFuse || kTmaStore, "the fused mode stores its tiles with TMA");
     extern __shared__ uint8_t smem_raw[];
     // 128B swizzle atoms need 1024-byte aligned tiles
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -161,6 +170,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     if (kCluster == 2) cluster_sync_all();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // fused mode: this call's generation (CTA 0 writes it back when the output is complete)
+    uint32_t fz_gen = 0;
+    if (kFuse) fz_gen = *(fz.arrived[fz.rank] + fz.tiles_per_owner + 1) + 1;
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -283,7 +295,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 }
             }
         }
-    } else if (warp >= kEpiWarp0) {
+    } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + 4) {
         // ===================== epilogue =====================
         const int ew = warp - kEpiWarp0;  // == warp % 4: TMEM lane quadrant
         int acc = 0;
@@ -392,6 +404,19 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     else
                         mbar_arrive(&tmem_empty[acc]);
                 }
+                if (kFuse) {
+                    // my 32 rows of the tile are in this GPU's copy: tell the tile's owner
+                    if (lane == 0 && m0 < M) {
+                        bulk_wait_all();
+                        asm volatile("fence.proxy.async;" ::: "memory");
+                        fence_acq_rel_sys();
+                        // owner and slot follow the PRODUCTION order (the same on every rank):
+                        // the reducers then meet their tiles in the order they complete
+                        const int q = t * kCluster + crank;
+                        fuse_red_release_sys(fz.arrived[q % fz.world] + q / fz.world, 1u);
+                    }
+                    __syncwarp();
+                }
                 if (++acc == 2) {
                     acc = 0;
                     acc_phase ^= 1;
@@ -463,6 +488,86 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 acc_phase ^= 1;
             }
         }
+        }
+    }
+
+    if (kFuse && warp >= kFuseRedWarp0) {
+        // ===================== reducers (fused mode), concurrent with the GEMM warps ==========
+        const int rt = threadIdx.x - kFuseRedWarp0 * 32;
+        const int W = fz.world;
+        const int real_tiles = m_blocks * n_blocks;
+        uint32_t* my_arrived = fz.arrived[fz.rank];
+        // Tiles in production order q = t * kCluster + crank; this rank owns q = j * W + rank.
+        // A unit of reducer work is one 32-row slab of an owned tile, units dealt round-robin
+        // over the CTAs: a few owned tiles still keep many SMs' worth of requests in flight.
+        const int seq = num_tiles * kCluster;
+        const int owned = (seq - fz.rank + W - 1) / W;
+        bool alive = true;
+        for (int unit = blockIdx.x; unit < owned * 4 && alive; unit += gridDim.x) {
+            const int j = unit >> 2, slab = unit & 3;
+            const int q = j * W + fz.rank;
+            int mb, nb;
+            tile_coords_rt(q / kCluster, m_units, n_blocks, group_m, mb, nb);
+            const int r0 = (mb * kCluster + q % kCluster) * BLOCK_M + slab * 32;
+            const int c0 = nb * BN;
+            if ((mb * kCluster + q % kCluster) * BLOCK_M >= M) continue;   // no such tile
+            if (rt == 0) {
+                const uint32_t target = fz_gen * 4u * (uint32_t)W;   // 4 epilogue warps per rank
+                const long long t0 = clock64();
+                while ((int32_t)(ld_acquire_sys_u32(my_arrived + j) - target) < 0) {
+                    if (clock64() - t0 > fz.timeout) {
+                        atomicExch(fz.err, 1u);
+                        break;
+                    }
+                }
+            }
+            fuse_reducer_bar();
+            if (*(volatile uint32_t*)fz.err != 0u) alive = false;     // a peer never arrived
+            constexpr int kVecs = 32 * BN / 8;
+            constexpr int UN = kVecs / 128 < 4 ? kVecs / 128 : 4;
+            for (int v0 = rt; alive && v0 < kVecs; v0 += 128 * UN) {
+                uint4 r[UN];
+                size_t off[UN];
+                bool ok[UN];
+#pragma unroll
+                for (int u = 0; u < UN; ++u) {
+                    const int v = v0 + u * 128;
+                    const int gr = r0 + v / (BN / 8), gc = c0 + (v % (BN / 8)) * 8;
+                    ok[u] = gr < M && gc < N;
+                    off[u] = ((size_t)gr * fz.ldo + gc) * 2;
+                    if (ok[u]) r[u] = fuse_mm_ld_reduce_bf16x8(fz.mc_out + off[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < UN; ++u) {
+                    if (!ok[u]) continue;
+                    if (fz.scale != 1.f) {
+                        float f[8];
+                        bf16x8_to_f32(*reinterpret_cast<bf16x8*>(&r[u]), f);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) f[i] *= fz.scale;
+                        bf16x8 pk = f32_to_bf16x8(f);
+                        r[u] = *reinterpret_cast<uint4*>(&pk);
+                    }
+                    fuse_mm_st_16(fz.mc_out + off[u], r[u]);
+                }
+            }
+            fuse_reducer_bar();
+            if (alive && rt < W) {
+                fence_acq_rel_sys();
+                fuse_red_release_sys(fz.arrived[rt] + fz.tiles_per_owner, 1u);   // delivered
+            }
+        }
+        if (blockIdx.x == 0 && rt == 0) {
+            uint32_t* my_delivered = my_arrived + fz.tiles_per_owner;
+            const uint32_t target = fz_gen * (uint32_t)real_tiles * 4u;   // slabs
+            const long long t0 = clock64();
+            while ((int32_t)(ld_acquire_sys_u32(my_delivered) - target) < 0) {
+                if (clock64() - t0 > fz.timeout || *(volatile uint32_t*)fz.err != 0u) {
+                    atomicExch(fz.err, 1u);
+                    break;
+                }
+            }
+            my_delivered[1] = fz_gen;
         }
     }
 
@@ -662,7 +767,59 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
         if (group_m > m_units) group_m = m_units;
     }
     TFOP_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, C, bias, bias_dtype, M, N, K, ldc,
-                                 out_dtype, epi, a_mn, b_mn, group_m, splits));
+                                 out_dtype, epi, a_mn, b_mn, group_m, splits, GemmFuse{}));
+    return 0;
+}
+
+// Fused GEMM -> in-switch all-reduce: the 2-CTA kernel with the reducer warps. Every CTA of every
+// rank must be resident at once (the reducers wait for the other ranks' tiles).
+template <int BN>
+int launch_fused(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, void* C,
+                 int M, int N, int K, int ldc, int a_mn, int b_mn, const GemmFuse& fz, int max_ctas_req,
+                 cudaStream_t stream) {
+    static int max_ctas_dev[kMaxDevices] = {};
+    auto kern = gemm_tn_kernel<BN, true, 2, true>;
+    int dev = 0, sms = 0;
+    if (current_device(&dev) != 0 || num_sms(&sms) != 0) return -1;
+    int& max_ctas = max_ctas_dev[dev];
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    if (max_ctas == 0) {
+        TFOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<BN, 2>::kSmemBytes));
+        cudaLaunchConfig_t q = {};
+        q.gridDim = dim3(sms / 2 * 2);
+        q.blockDim = dim3(kFuseThreads);
+        q.dynamicSmemBytes = Cfg<BN, 2>::kSmemBytes;
+        q.attrs = attr;
+        q.numAttrs = 1;
+        int n = 0;
+        TFOP_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &q));
+        TFOP_REQUIRE(n > 0, "no 2-CTA cluster of the fused GEMM kernel fits on this device");
+        max_ctas = 2 * n;
+    }
+    const int m_units = ((M + BLOCK_M - 1) / BLOCK_M + 1) / 2;
+    const int units = m_units * ((N + BN - 1) / BN);
+    int grid = units * 2;
+    if (grid > max_ctas) grid = max_ctas;
+    if (max_ctas_req > 0 && grid > max_ctas_req) grid = max_ctas_req / 2 * 2;
+    if (grid < 2) grid = 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kFuseThreads);
+    cfg.dynamicSmemBytes = Cfg<BN, 2>::kSmemBytes;
+    cfg.stream = stream;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const long panel_row_bytes = (long)BLOCK_M * 2 * K * 2;
+    int group_m = (int)((32L << 20) / panel_row_bytes);
+    if (group_m < 2) group_m = 2;
+    if (group_m > m_units) group_m = m_units;
+    TFOP_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, C, (const void*)nullptr, 0, M, N, K, ldc,
+                                 (int)TFOP_BF16, (int)EPI_NONE, a_mn, b_mn, group_m, 1, fz));
     return 0;
 }
 
@@ -675,6 +832,23 @@ int tfop_gemm_make_tensor_map(CUtensorMap* map, const void* base, int rows, int 
     return make_map(map, base, rows, K, ld, box_rows);
 }
 int tfop_gemm_num_sms(int* out) { return num_sms(out); }
+
+// The fused GEMM -> in-switch all-reduce launch (gemm_allreduce.cu owns the protocol state).
+// C_local: this rank's copy of the multicast-bound output region, [M, N] bf16, row pitch ldo.
+// tile_n 128 or 256; a_mn / b_mn as in tfop_gemm_bf16.
+int tfop_gemm_launch_fused(const void* A, const void* B, void* C_local, int M, int N, int K,
+                           int lda, int ldb, int ldo, int a_mn, int b_mn, int tile_n,
+                           const tfop_gemm::GemmFuse* fz, int max_ctas, cudaStream_t stream) {
+    if (get_encode() != 0) return -1;
+    CUtensorMap ma, mb, mc;
+    if (a_mn ? make_map(&ma, A, K, M, lda, BLOCK_K) : make_map(&ma, A, M, K, lda, BLOCK_M)) return -1;
+    if (b_mn ? make_map(&mb, B, K, N, ldb, BLOCK_K) : make_map(&mb, B, N, K, ldb, tile_n / 2))
+        return -1;
+    if (make_map_c(&mc, C_local, M, N, ldo, TFOP_BF16) != 0) return -1;
+    if (tile_n == 256)
+        return launch_fused<256>(ma, mb, mc, C_local, M, N, K, ldo, a_mn, b_mn, *fz, max_ctas, stream);
+    return launch_fused<128>(ma, mb, mc, C_local, M, N, K, ldo, a_mn, b_mn, *fz, max_ctas, stream);
+}
 
 // C[M,N] = epi(op(A) * op(B)^T + bias[N]), bf16 operands, fp32 accumulation in TMEM.
 //   a_mn = 0: A is [M, K] row-major (K-major), lda elements between rows

@@ -98,6 +98,12 @@ _SIGS = {
     "tfop_gemm_allreduce_nvls_bf16_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                                  c_int, c_int, c_int, c_float, c_size_t, c_size_t,
                                                  c_int, c_void_p]),
+    "tfop_gemm_allreduce_nvls_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                              c_int, c_int, c_int, c_int, c_int, c_float, c_size_t,
+                                              c_size_t, c_int, c_void_p]),
+    "tfop_gemm_allreduce_nvls_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "tfop_gemm_allreduce_set_tile_n": (c_int, [c_int]),
+    "tfop_gemm_allreduce_set_legacy": (c_int, [c_int]),
     "tfop_gemm_allreduce_emulated": (c_int, [C.POINTER(c_void_p), c_int, C.POINTER(c_void_p),
                                              C.POINTER(c_void_p), c_int, c_int, c_int, c_int, c_int,
                                              c_int, c_float, c_size_t, c_size_t, c_void_p]),

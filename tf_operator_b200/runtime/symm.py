@@ -290,19 +290,31 @@ class SymmetricComm:
 
     def gemm_all_reduce_nvls(self, a: torch.Tensor, b: torch.Tensor, *, ws_off: int, out_off: int = 0,
                              ldo: Optional[int] = None, scale: float = 1.0, max_ctas: int = 0,
-                             stream=None) -> torch.Tensor:
-        """Fused GEMM + in-switch all-reduce; the result is this rank's view of the NVLS buffer."""
+                             a_mn: bool = False, b_mn: bool = False, stream=None) -> torch.Tensor:
+        """out = scale * sum over ranks of op(a_r) @ op(b_r)^T, ONE kernel: the cta_group::2
+        tcgen05 GEMM stores its partial tiles locally and the NVSwitch sums / broadcasts them as
+        they complete (csrc/gemm_allreduce.cu, NVLS flavour). ``a`` is [M, K] (or [K, M] with
+        ``a_mn``), ``b`` is [N, K] (or [K, N] with ``b_mn``): (True, True) is the weight gradient
+        dY^T X from the stored activations. The result is this rank's view of the NVLS buffer at
+        ``out_off``; ``ws_off`` names ``gemm_allreduce_nvls_workspace_bytes`` zeroed bytes of the
+        symmetric buffer, tied to this (M, N)."""
+        assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
         a = a if a.stride(1) == 1 and a.stride(0) % 8 == 0 else a.contiguous()
         b = b if b.stride(1) == 1 and b.stride(0) % 8 == 0 else b.contiguous()
-        m, k = a.shape
-        n = b.shape[0]
+        (k, m) = a.shape if a_mn else a.shape[::-1]
+        (kb, n) = b.shape if b_mn else b.shape[::-1]
+        assert k == kb, "contraction lengths differ"
         ldo = ldo or n
-        _lib.check(self._lib.tfop_gemm_allreduce_nvls_bf16_tn(
+        _lib.check(self._lib.tfop_gemm_allreduce_nvls_bf16(
             self._h, a.data_ptr(), b.data_ptr(), m, n, k, a.stride(0), b.stride(0), ldo,
-            float(scale), ws_off, out_off, max_ctas, _lib.stream_handle(stream)),
-            "gemm_allreduce_nvls")
+            int(a_mn), int(b_mn), float(scale), ws_off, out_off, max_ctas,
+            _lib.stream_handle(stream)), "gemm_allreduce_nvls")
         flat = self.nvls_view((m - 1) * ldo + n, torch.bfloat16, out_off)
         return torch.as_strided(flat, (m, n), (ldo, 1))
+
+    @staticmethod
+    def gemm_allreduce_nvls_workspace_bytes(m: int, n: int, world: int) -> int:
+        return _lib.load().tfop_gemm_allreduce_nvls_workspace_bytes(m, n, world)
 
     def set_timeout_ms(self, ms: int) -> None:
         """Spin limit of the flag barriers (default 120 s). Process-wide; applies to collectives
