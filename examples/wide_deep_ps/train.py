@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--batch-size", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--profile", action="store_true", help="print the step's kernels (torch profiler)")
     args = ap.parse_args()
 
     ctx = ReplicaContext.from_env()
@@ -71,6 +72,8 @@ def main():
         rdv.barrier(prefix + "/shards-ready", world)
         if is_ps:
             # server.join(): the shard lives in this process's HBM until the job is cleaned up
+            # (cleanPodPolicy Running). Nothing runs here: the workers read and update the shard
+            # over NVLink, and an idle owner serves them at full speed (benchmarks/ps_bench.py).
             while True:
                 time.sleep(3600)
         ps_ranks = list(range(n_ps))
@@ -103,6 +106,35 @@ def main():
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
+    if args.profile:
+        import subprocess
+        for _ in range(5):
+            deep.gather(torch.zeros(8, dtype=torch.int64, device=dev), torch.bfloat16)
+        ids0 = batch()[0]
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(10):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            deep.gather(ids0, torch.bfloat16)
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(round(a.elapsed_time(b) * 1e3, 1))
+        print("standalone deep gather us:", ts, flush=True)
+        print(subprocess.run(["nvidia-smi", "--query-gpu=index,pstate,clocks.sm,clocks.mem,power.draw,"
+                              "utilization.gpu", "--format=csv"], capture_output=True, text=True).stdout,
+              flush=True)
+        print("CUDA_VISIBLE_DEVICES", os.environ.get("CUDA_VISIBLE_DEVICES"), "ptr",
+              hex(deep.table.weight[0]), flush=True)
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            for _ in range(5):
+                step()
+            torch.cuda.synchronize()
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=25, max_name_column_width=70),
+              flush=True)
+        print(prof.key_averages().table(sort_by="cpu_time_total", row_limit=12, max_name_column_width=70),
+              flush=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):

@@ -195,6 +195,7 @@ int tfop_ps_push_adagrad(const tfop_ps_table* table, const void* uniq_ids_i64,
  * four kernels, no sort, no host round trip, no allocation). ids as the batch names them
  * (negative = padding). The six scratch arrays are sized by tfop_ps_dedup_workspace; before the
  * first use fill keys with 0xFF and the rest with zero - every call leaves them in that state. */
+int tfop_ps_set_push_mode(int fetch);   /* 1: fetch-and-add accumulators; 0 (default): load + RED */
 int tfop_ps_dedup_workspace(size_t n_ids, int dim, size_t* sizes6);
 int tfop_ps_push_adagrad_dedup(const tfop_ps_table* table, const void* ids_i64, size_t n_ids,
                                const void* grad, int grad_dtype, float lr, float eps,

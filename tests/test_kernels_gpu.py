@@ -304,10 +304,9 @@ def test_ps_push_merges_duplicates_on_the_device_and_leaves_its_scratch_clean(de
         a.push(ids, g, stream=st)                  # warm: the scratch exists before capture
         with torch.cuda.graph(graph, stream=st):
             a.push(ids, g, stream=st)
-    b.push_sorted(ids, g)
-    b.push_sorted(ids, g)
+    b.push_sorted(ids, g)            # the warm-up call above
     graph.replay()
-    b.push_sorted(ids, g)
+    b.push_sorted(ids, g)            # the replay
     torch.cuda.synchronize()
     for x, y in zip(a.shards + a.accums, b.shards + b.accums):
         torch.testing.assert_close(x, y, rtol=1e-4, atol=1e-5)

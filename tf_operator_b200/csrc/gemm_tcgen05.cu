@@ -503,6 +503,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         const int seq = num_tiles * kCluster;
         const int owned = (seq - fz.rank + W - 1) / W;
         bool alive = true;
+        int done = 0;
         for (int unit = blockIdx.x; unit < owned * 4 && alive; unit += gridDim.x) {
             const int j = unit >> 2, slab = unit & 3;
             const int q = j * W + fz.rank;
@@ -523,8 +524,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
             fuse_reducer_bar();
             if (*(volatile uint32_t*)fz.err != 0u) alive = false;     // a peer never arrived
+            // the whole slab in one round: 16 bytes x UN per thread in flight through the switch
             constexpr int kVecs = 32 * BN / 8;
-            constexpr int UN = kVecs / 128 < 4 ? kVecs / 128 : 4;
+            constexpr int UN = kVecs / 128;
             for (int v0 = rt; alive && v0 < kVecs; v0 += 128 * UN) {
                 uint4 r[UN];
                 size_t off[UN];
@@ -551,11 +553,13 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     fuse_mm_st_16(fz.mc_out + off[u], r[u]);
                 }
             }
-            fuse_reducer_bar();
-            if (alive && rt < W) {
-                fence_acq_rel_sys();
-                fuse_red_release_sys(fz.arrived[rt] + fz.tiles_per_owner, 1u);   // delivered
-            }
+            if (alive) ++done;
+        }
+        // one release per CTA, not per slab: every rank learns how many slabs this CTA delivered
+        fuse_reducer_bar();
+        if (done > 0 && rt < W) {
+            fence_acq_rel_sys();
+            fuse_red_release_sys(fz.arrived[rt] + fz.tiles_per_owner, (uint32_t)done);
         }
         if (blockIdx.x == 0 && rt == 0) {
             uint32_t* my_delivered = my_arrived + fz.tiles_per_owner;

@@ -231,6 +231,14 @@ __global__ void __launch_bounds__(256) ps_dedup_sum_kernel(
     }
 }
 
+// kFetch: the accumulator update is a fetch-and-add (exact under concurrent pushes of the same
+// row by several workers, one NVLink round trip per 16 bytes that nothing can overlap). !kFetch:
+// the old accumulator is read with a plain peer load (pipelines like the gather), the two
+// updates leave as fire-and-forget reductions; a concurrent push of the same row by another
+// worker may then scale its step with an accumulator that misses this one's g^2 - the staleness
+// asynchronous PS training has anyway (the reference's workers apply gradients computed on
+// stale variables, examples/v1/dist-mnist/dist_mnist.py:161-208).
+template <bool kFetch>
 __global__ void __launch_bounds__(256) ps_dedup_apply_kernel(
     const tfop_ps_table t, const long long* __restrict__ uniq, const int* __restrict__ count,
     float* __restrict__ sums, float lr, float eps, float grad_scale) {
@@ -250,7 +258,13 @@ __global__ void __launch_bounds__(256) ps_dedup_apply_kernel(
         g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
         const size_t off = (size_t)row * t.dim + (size_t)c * 4;
         const float4 sq = make_float4(g.x * g.x, g.y * g.y, g.z * g.z, g.w * g.w);
-        const float4 old = atom_add_f4_sys(t.accum[shard] + off, sq);
+        float4 old;
+        if (kFetch) {
+            old = atom_add_f4_sys(t.accum[shard] + off, sq);
+        } else {
+            old = ld_peer_f4(t.accum[shard] + off);
+            red_add_f4_sys(t.accum[shard] + off, sq);
+        }
         float4 d;
         d.x = -lr * g.x / (sqrtf(old.x + sq.x) + eps);
         d.y = -lr * g.y / (sqrtf(old.y + sq.y) + eps);
@@ -259,6 +273,8 @@ __global__ void __launch_bounds__(256) ps_dedup_apply_kernel(
         red_add_f4_sys(t.weight[shard] + off, d);
     }
 }
+
+int g_push_fetch = 0;   // tfop_ps_set_push_mode
 
 size_t dedup_capacity(size_t n_ids) {
     size_t cap = 1024;
@@ -368,9 +384,21 @@ TFOP_API int tfop_ps_push_adagrad_dedup(const tfop_ps_table* table, const void* 
     else
         ps_dedup_sum_kernel<false><<<grid, 256, 0, stream>>>(
             (const int*)ws_slot_of, (const int*)ws_dense, n_ids, table->dim, grad, (float*)ws_sums);
-    ps_dedup_apply_kernel<<<grid, 256, 0, stream>>>(*table, (const long long*)ws_uniq,
-                                                    (const int*)ws_count, (float*)ws_sums, lr,
-                                                    eps, grad_scale);
+    if (g_push_fetch)
+        ps_dedup_apply_kernel<true><<<grid, 256, 0, stream>>>(
+            *table, (const long long*)ws_uniq, (const int*)ws_count, (float*)ws_sums, lr, eps,
+            grad_scale);
+    else
+        ps_dedup_apply_kernel<false><<<grid, 256, 0, stream>>>(
+            *table, (const long long*)ws_uniq, (const int*)ws_count, (float*)ws_sums, lr, eps,
+            grad_scale);
     TFOP_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// 1: fetch-and-add on the accumulator (exact under concurrent pushes of one row); 0 (default):
+// plain load + two fire-and-forget reductions (see ps_dedup_apply_kernel).
+TFOP_API int tfop_ps_set_push_mode(int fetch) {
+    g_push_fetch = fetch ? 1 : 0;
     return 0;
 }

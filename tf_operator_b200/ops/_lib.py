@@ -139,6 +139,7 @@ _SIGS = {
     "tfop_ps_push_adagrad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p,
                                      c_int, c_float, c_float, c_float, c_int, c_void_p]),
     "tfop_ps_dedup_workspace": (c_int, [c_size_t, c_int, c_void_p]),
+    "tfop_ps_set_push_mode": (c_int, [c_int]),
     "tfop_ps_push_adagrad_dedup": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_float,
                                            c_float, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                                            c_void_p, c_void_p, c_int, c_void_p]),
