@@ -149,7 +149,10 @@ def test_same_named_job_submitted_twice_trains_both_times(cluster, tmp_path):
         assert cluster.rendezvous.keys(f"default/mg-twice/{uid}/") == []
     for r in results:
         assert r["world"] == WORLD and r["generation"] == 0 and r["final_loss"] == r["final_loss"]
-    assert results[0]["final_loss"] == pytest.approx(results[1]["final_loss"], abs=1e-3)
+    # same data, same seeds; the reductions (fp32 atomics in the statistics and weight-gradient
+    # kernels) are not ordered, so the two runs agree closely, not bit for bit
+    assert results[0]["final_loss"] == pytest.approx(results[1]["final_loss"], abs=2e-2)
+    assert max(r["final_loss"] for r in results) < 0.5
 
 
 def test_killed_replica_reforms_the_gang_and_training_resumes(cluster, tmp_path):
