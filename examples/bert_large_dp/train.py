@@ -30,6 +30,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "nccl"])
     ap.add_argument("--no-graph", action="store_true", help="run eager instead of one CUDA graph per step")
+    ap.add_argument("--fused-wgrad", action="store_true",
+                    help="weight gradients of the encoder's linear layers: GEMM and cross-rank sum in "
+                         "ONE kernel (in-switch reduction) instead of GEMM + bucket all-reduce")
     ap.add_argument("--no-nvls", action="store_true",
                     help="reduce gradient buckets with the P2P two-shot kernel instead of NVLS multimem")
     ap.add_argument("--ckpt", default="", help="checkpoint file (a mounted path in the pod template): "
@@ -74,7 +77,8 @@ def main():
                                       nvls_bytes=0 if args.no_nvls else nparam * 2 + (1 << 20))
         use_nvls = comm is not None and getattr(comm, "nvls_bytes", 0) > 0
         dp = FlatDataParallel(model, comm=comm, optimizer="adamw", lr=1e-4, weight_decay=0.01,
-                              bucket_bytes=64 << 20, use_nvls=use_nvls)
+                              bucket_bytes=64 << 20, use_nvls=use_nvls,
+                              fused_wgrad=args.fused_wgrad)
 
         if args.ckpt and os.path.exists(args.ckpt):
             print(json.dumps({"resumed_from_step": dp.load_checkpoint(args.ckpt)}), flush=True)
@@ -121,6 +125,7 @@ def main():
            "per_gpu_batch": B, "ms_per_step": round(ms, 3),
            "seq_per_s_job": round(B * ctx.world_size / ms * 1e3, 1), "loss": round(float(loss), 4),
            "kernel_launches_per_step": launches(),
+           "fused_wgrad": bool(getattr(dp, "fused_wgrad", False)) if args.impl == "native" else False,
            "allreduce": ("nvls" if (args.impl == "native" and ctx.world_size > 1 and use_nvls) else
                          "p2p two-shot" if (args.impl == "native" and ctx.world_size > 1) else
                          "nccl" if ctx.world_size > 1 else None)}

@@ -83,3 +83,22 @@ def test_import_named_reports_missing_and_shape_errors():
     bad[first] = torch.zeros(3)
     with pytest.raises(ValueError):
         fp.import_named(fp.master, bad)
+
+
+def test_fused_region_comes_first_and_belongs_to_no_bucket():
+    """FlatParams(fused=[...]): parameters whose gradient arrives already summed over the ranks
+    (GradTarget.fused) sit at the front of the flat buffers, outside every bucket; the rest is
+    bucketed as before and the decay / no-decay boundary does not move."""
+    import torch.nn as nn
+    m = nn.Sequential(nn.Linear(64, 128), nn.Linear(128, 32), nn.LayerNorm(32), nn.Linear(32, 8))
+    fused = [m[0].weight, m[1].weight]
+    fp = FlatParams(m, torch.device("cpu"), bucket_bytes=1 << 10, fused=fused)
+    plain = FlatParams(nn.Sequential(nn.Linear(64, 128), nn.Linear(128, 32), nn.LayerNorm(32), nn.Linear(32, 8)),
+                       torch.device("cpu"), bucket_bytes=1 << 10)
+    assert fp.total == plain.total and fp.n_decay == plain.n_decay
+    assert fp.n_fused == 64 * 128 + 128 * 32
+    assert {id(s.param) for s in fp.slots if s.offset < fp.n_fused} == {id(p) for p in fused}
+    assert all(fp.bucket_of(p) is None for p in fused)
+    assert fp.buckets[0].lo == fp.n_fused and fp.buckets[-1].hi == fp.total
+    assert sum(len(b.slots) for b in fp.buckets) == len(fp.slots) - 2
+    assert fp.bucket_of(m[3].weight) is not None and plain.n_fused == 0

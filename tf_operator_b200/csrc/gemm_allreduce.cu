@@ -543,12 +543,12 @@ TFOP_API int tfop_gemm_allreduce_nvls_bf16(tfop_comm* c, const void* A, const vo
     int sms = 0;
     if (tfop_gemm_num_sms(&sms) != 0) return -1;
     if (!legacy) {
-        // wide tiles when they fill the machine; narrower ones otherwise, so that the first
-        // wave's tiles travel while the second wave multiplies
+        // wide tiles unless they would leave most of the machine idle (measured on 8 GPUs:
+        // 256 wins from 48 tile pairs up, 128 at 16 - r2_gemm_allreduce_8gpu.json)
         int tile_n = g_nvls_tile_n;
         if (tile_n == 0) {
             const long pairs256 = (long)((m_blocks + 1) / 2) * ((N + 255) / 256);
-            tile_n = (N >= 256 && pairs256 >= sms / 2) ? 256 : 128;
+            tile_n = (N >= 256 && pairs256 >= 32) ? 256 : 128;
         }
         // tiles are owned by production sequence number: 2 per scheduling unit (CTA pair)
         const int tiles = (m_blocks + 1) / 2 * 2 * ((N + tile_n - 1) / tile_n);

@@ -137,8 +137,16 @@ class _LinearFn(torch.autograd.Function):
             # a flat-buffer engine lets the GEMM store dW straight into the gradient bucket
             target = getattr(w, "_tfop_grad_target", None)
             out = target.take() if (target is not None and mn_ok and w.dtype == torch.bfloat16) else None
-            dw = (gemm(dy2, x2, a_t=True, b_t=True, out=out) if mn_ok
-                  else gemm_tn(transpose(dy2), transpose(x2)))
+            if out is not None and target.fused is not None:
+                # data-parallel job: dW is produced and summed over the ranks by one kernel,
+                # in place in the multicast-bound gradient buffer (the engine's fused_wgrad)
+                comm, ws_off, scale, base = target.fused
+                comm.gemm_all_reduce_nvls(dy2, x2, a_mn=True, b_mn=True, ws_off=ws_off, scale=scale,
+                                          out_off=out.data_ptr() - base)
+                dw = out
+            else:
+                dw = (gemm(dy2, x2, a_t=True, b_t=True, out=out) if mn_ok
+                      else gemm_tn(transpose(dy2), transpose(x2)))
         if ctx.has_bias and ctx.needs_input_grad[2]:
             from .layernorm import bias_grad
             db = bias_grad(dy2)

@@ -59,7 +59,7 @@ class FlatDataParallel:
                  weight_decay: float = 1e-4, nesterov: bool = False, betas=(0.9, 0.999),
                  eps: float = 1e-8, bucket_bytes: int = 16 << 20, overlap: bool = True,
                  comm_blocks: int = 32, device: Optional[torch.device] = None,
-                 channels_last: bool = False, use_nvls: bool = False):
+                 channels_last: bool = False, use_nvls: bool = False, fused_wgrad: bool = False):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.comm = comm
         self.world = comm.world if comm is not None else 1
@@ -81,7 +81,35 @@ class FlatDataParallel:
             else:
                 assert comm.nbytes >= total * 2, "symmetric buffer too small for the gradient bucket"
                 grad_buf = comm.view(0, total, torch.bfloat16)
-        self.flat = FlatParams(model, self.device, grad_buffer=grad_buf, bucket_bytes=bucket_bytes)
+        # fused_wgrad: the weight gradient of every once-used TcLinear is computed and summed over
+        # the ranks by ONE kernel (GEMM -> in-switch reduction, csrc/gemm_allreduce.cu) straight into
+        # its slot of the multicast-bound gradient buffer; those slots belong to no bucket
+        fused = []
+        if fused_wgrad and self.use_nvls and self.world > 1:
+            from ..ops.gemm import TcLinear
+            owners = {}                       # a weight tied to another module is used twice
+            for m in model.modules():
+                for p in m.parameters(recurse=False):
+                    owners[id(p)] = owners.get(id(p), 0) + 1
+            for m in model.modules():
+                if isinstance(m, TcLinear) and owners.get(id(m.weight), 0) == 1 and \
+                        m.weight.requires_grad and m.out_features >= 256 and \
+                        m.out_features % 8 == 0 and m.in_features % 8 == 0:
+                    fused.append(m.weight)
+        self.flat = FlatParams(model, self.device, grad_buffer=grad_buf, bucket_bytes=bucket_bytes,
+                               fused=fused)
+        self.fused_wgrad = bool(fused)
+        if fused:
+            ws = 0
+            for s in self.flat.slots:
+                if s.offset >= self.flat.n_fused:
+                    continue
+                m, n = s.param.shape
+                assert s.param.is_contiguous()
+                s.param._tfop_grad_target.fused = (comm, ws, 1.0 / self.world,
+                                                   comm._lib.tfop_nvls_local_ptr(comm._h))
+                ws += SymmetricComm.gemm_allreduce_nvls_workspace_bytes(m, n, self.world)
+            assert ws <= comm.nbytes, "symmetric buffer too small for the fused-wgrad counters"
         self.mom = torch.zeros(self.flat.total, dtype=torch.float32, device=self.device)
         self.mom2 = torch.zeros(self.flat.total, dtype=torch.float32, device=self.device) \
             if optimizer == "adamw" else None
@@ -117,6 +145,8 @@ class FlatDataParallel:
             if not self.overlap or not self._in_backward:
                 return
             b = self.flat.bucket_of(p)
+            if b is None:
+                return                        # fused region: already summed by its own kernel
             with self._hook_lock:
                 b.pending -= 1
                 fire = b.pending == 0

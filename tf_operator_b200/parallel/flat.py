@@ -16,7 +16,7 @@ examples/v1/distribution_strategy/keras-API/multi_worker_strategy-with-keras.py:
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import List, Optional
+from typing import List, Optional, Sequence
 
 import torch
 import torch.nn as nn
@@ -53,6 +53,9 @@ class GradTarget:
 
     def __init__(self, flat: "FlatParams", slot: "Slot"):
         self.flat, self.slot, self.used_step = flat, slot, -1
+        # (comm, ws_off, scale) when this parameter's weight gradient is produced AND summed over
+        # the ranks by one kernel (SymmetricComm.gemm_all_reduce_nvls) straight into its slot
+        self.fused = None
 
     def take(self) -> Optional[torch.Tensor]:
         if self.used_step == self.flat.step_id:
@@ -64,16 +67,26 @@ class GradTarget:
 
 class FlatParams:
     def __init__(self, model: nn.Module, device: torch.device, *, grad_buffer: Optional[torch.Tensor] = None,
-                 bucket_bytes: int = 16 << 20, weight_dtype: torch.dtype = torch.bfloat16):
+                 bucket_bytes: int = 16 << 20, weight_dtype: torch.dtype = torch.bfloat16,
+                 fused: Optional[Sequence[nn.Parameter]] = None):
+        """``fused``: parameters whose gradient arrives already summed over the ranks (see
+        GradTarget.fused). They get the front of the flat buffers and belong to no bucket."""
         named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
-        decay = [(n, p) for n, p in named if p.ndim > 1]
+        fused_ids = {id(p) for p in (fused or [])}
+        decay = [(n, p) for n, p in named if p.ndim > 1 and id(p) not in fused_ids]
+        fused_named = [(n, p) for n, p in named if id(p) in fused_ids]
+        assert all(p.ndim > 1 for _, p in fused_named), "only weight matrices can be fused"
         nodecay = [(n, p) for n, p in named if p.ndim <= 1]
         self.slots: List[Slot] = []
         off = 0
-        for group, is_decay in ((decay[::-1], True), (nodecay[::-1], False)):
+        self.n_fused = 0
+        for gi, (group, is_decay) in enumerate(((fused_named[::-1], True), (decay[::-1], True),
+                                                (nodecay[::-1], False))):
             for n, p in group:
                 self.slots.append(Slot(n, p, off, p.numel(), is_decay))
                 off += _pad8(p.numel())
+            if gi == 0:
+                self.n_fused = off
             if is_decay:
                 self.n_decay = off
         self.total = off
@@ -107,6 +120,8 @@ class FlatParams:
         cur = None
         limit = max(1, bucket_bytes // 2)
         for s in self.slots:
+            if s.offset < self.n_fused:
+                continue                      # reduced by the kernel that produces it
             if cur is None or (s.decay and cur.hi - cur.lo >= limit):
                 cur = Bucket(s.offset, s.offset)
                 self.buckets.append(cur)
@@ -126,8 +141,9 @@ class FlatParams:
         g = s.param.grad
         return g is not None and g.data_ptr() == self.grads.data_ptr() + s.offset * self.grads.element_size()
 
-    def bucket_of(self, p: nn.Parameter) -> Bucket:
-        return self._bucket_of[id(p)]
+    def bucket_of(self, p: nn.Parameter) -> Optional[Bucket]:
+        """None for a parameter of the fused region."""
+        return self._bucket_of.get(id(p))
 
     def grad_view(self, s: Slot) -> torch.Tensor:
         p = s.param
