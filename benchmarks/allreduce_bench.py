@@ -42,6 +42,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
     ap.add_argument("--max-mb", type=int, default=256)
+    ap.add_argument("--link-bytes", action="store_true",
+                    help="also read the NVLink data counters (nvidia-smi nvlink -gt d) around 200 calls "
+                         "at 64 MB, and sweep the block count of the in-switch all-reduce")
     args = ap.parse_args()
     rank = int(os.environ["RANK"])
     world = int(os.environ["WORLD_SIZE"])
@@ -128,6 +131,64 @@ def main():
         row["nccl"] = {"us": round(us, 2),
                        "busbw_GBps": round(2 * (world - 1) / world * nbytes / us / 1e3, 1)}
         results["rows"].append(row)
+    # ---- traffic evidence: NVLink data counters of this rank's GPU around 200 calls at 64 MB ----
+    if args.link_bytes:
+        import re
+        import subprocess
+
+        def link_kib():
+            try:
+                txt = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(local)],
+                                     capture_output=True, text=True, timeout=30).stdout
+            except Exception as e:  # noqa: BLE001
+                return None, None, repr(e)
+            tx = sum(int(v) for v in re.findall(r"Data Tx:\s*(\d+)\s*KiB", txt))
+            rx = sum(int(v) for v in re.findall(r"Data Rx:\s*(\d+)\s*KiB", txt))
+            return tx, rx, ("" if (tx or rx) else txt[-300:])
+        nbytes = 64 << 20
+        n = nbytes // 2
+        calls = 200
+        torch.manual_seed(100 + rank)
+        x = torch.randn(n, device=dev).bfloat16()
+        sym = comm.view(0, n, torch.bfloat16)
+        modes = [("twoshot_inplace", lambda: comm.all_reduce(n, sym_off=0, scale=1.0 / world, algo=TWO_SHOT),
+                  2.0 * (world - 1) / world * nbytes)]
+        if nvls:
+            nv = comm.nvls_view(n, torch.bfloat16)
+            nv.copy_(x)
+            modes.append(("nvls_inplace", lambda: comm.all_reduce_nvls(n, sym_off=0, scale=1.0 / world),
+                          (1.0 + 1.0 / world) * nbytes))
+        y = x.clone()
+        modes.append(("nccl", lambda: dist.all_reduce(y), None))
+        sym.copy_(x)
+        link = {"bytes": nbytes, "calls": calls, "gpu": local, "modes": {}}
+        for name, fn, algo_bytes in modes:
+            torch.cuda.synchronize()
+            dist.barrier()
+            tx0, rx0, note = link_kib()
+            dist.barrier()
+            for _ in range(calls):
+                fn()
+            torch.cuda.synchronize()
+            dist.barrier()
+            tx1, rx1, _ = link_kib()
+            dist.barrier()
+            rec = {"algorithmic_bytes_per_call_and_direction": algo_bytes}
+            if tx0 is None or note:
+                rec["counters"] = f"unavailable: {note}"
+            else:
+                rec["measured_tx_bytes_per_call"] = round((tx1 - tx0) * 1024 / calls)
+                rec["measured_rx_bytes_per_call"] = round((rx1 - rx0) * 1024 / calls)
+            link["modes"][name] = rec
+        results["nvlink_counters_rank0" if rank == 0 else "_"] = link
+        results.pop("_", None)
+        # block-count sweep of the in-switch all-reduce at 64 MB (cap: TFOP_MAX_BLOCKS = 64)
+        if nvls:
+            sweep = {}
+            for blocks in (8, 16, 32, 48, 64):
+                us = timed(lambda: comm.all_reduce_nvls(n, sym_off=0, scale=1.0 / world, max_blocks=blocks), 20)
+                sweep[str(blocks)] = round(us, 2)
+            results["nvls_inplace_64MB_us_by_blocks"] = sweep
     # fp32 histogram all-reduce (K6)
     h = torch.randn(hist_n, device=dev)
     href = h.clone()
