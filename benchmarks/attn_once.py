@@ -49,7 +49,7 @@ out = torch.empty((b, s_, h), dtype=torch.bfloat16, device="cuda")
 lse = torch.empty((b, a.heads, s_), dtype=torch.float32, device="cuda")
 dqkv = torch.empty_like(q)
 delta = torch.empty_like(lse)
-dq32 = torch.empty((b * s_, h), dtype=torch.float32, device="cuda")
+dq32 = torch.zeros((b * s_, h), dtype=torch.float32, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
 
 
@@ -70,4 +70,12 @@ tb = many(lambda: lib.tfop_attn_bwd(q.data_ptr(), out.data_ptr(), dout.data_ptr(
                                     dqkv.data_ptr(), delta.data_ptr(), dq32.data_ptr(), b, s_, a.heads, 64, st))
 print(f"kernel-only: fwd {tf:.1f} us ({flops / tf / 1e6:.0f} TFLOP/s)  bwd (memset + delta + main + convert) "
       f"{tb:.1f} us ({2.5 * flops / tb / 1e6:.0f} TFLOP/s)")
+from torch.profiler import ProfilerActivity, profile  # noqa: E402
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    for _ in range(10):
+        lib.tfop_attn_bwd(q.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
+                          dqkv.data_ptr(), delta.data_ptr(), dq32.data_ptr(), b, s_, a.heads, 64, st)
+    torch.cuda.synchronize()
+for e in sorted(prof.key_averages(), key=lambda e: -e.device_time_total)[:6]:
+    print(f"  {e.device_time_total / e.count:8.1f} us x{e.count}  {e.key[:90]}")
 print("ok")

@@ -214,40 +214,53 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, 
         for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
             int b, head, qb;
             decode(w, b, head, qb);
+            // Both passes keep ONE tcgen05.ld in flight while the previous chunk is being worked on
+            // (tcgen05.wait::ld waits for every outstanding load, so the next load is issued right
+            // after the wait and before the arithmetic): the first version waited out each load's
+            // full latency 24 times per tile.
             float m = -INFINITY;
-            for (int j = 0; j < nkb; ++j, ++T) {   // pass 1: exact row maximum
-                const int sb = (int)(T % kSBuf);
-                mbar_wait(&s_full[sb], (T / kSBuf) & 1u);
-                tcgen05_fence_after();
-                const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
-#pragma unroll 1
-                for (int c = 0; c < kBK; c += 64) {
-                    uint32_t r0[32], r1[32];
-                    tmem_ld_32x32b_x32(t_s + (uint32_t)c, r0);
-                    tmem_ld_32x32b_x32(t_s + (uint32_t)c + 32u, r1);
-                    tmem_ld_wait();
+            {   // pass 1: exact row maximum; half tiles of 64 keys ping-pong between A and B
+                uint32_t A0[32], A1[32], B0[32], B1[32];
+                {
+                    const int sb = (int)(T % kSBuf);
+                    mbar_wait(&s_full[sb], (T / kSBuf) & 1u);
+                    tcgen05_fence_after();
+                    const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
+                    tmem_ld_32x32b_x32(t_s, A0);
+                    tmem_ld_32x32b_x32(t_s + 32u, A1);
+                }
+                for (int j = 0; j < nkb; ++j, ++T) {
+                    const int sb = (int)(T % kSBuf);
+                    const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
+                    tmem_ld_wait();                                  // A: keys 0-63 of tile j
+                    tmem_ld_32x32b_x32(t_s + 64u, B0);
+                    tmem_ld_32x32b_x32(t_s + 96u, B1);
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
-                        m = fmaxf(m, fmaxf(__uint_as_float(r0[i]), __uint_as_float(r1[i])));
+                        m = fmaxf(m, fmaxf(__uint_as_float(A0[i]), __uint_as_float(A1[i])));
+                    tmem_ld_wait();                                  // B: every load of tile j is in
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_free[sb]);
+                    if (j + 1 < nkb) {
+                        const int sn = (int)((T + 1) % kSBuf);
+                        mbar_wait(&s_full[sn], ((T + 1) / kSBuf) & 1u);
+                        tcgen05_fence_after();
+                        const uint32_t t_n = tmem_base + (uint32_t)(sn * 128) + lane_sel;
+                        tmem_ld_32x32b_x32(t_n, A0);
+                        tmem_ld_32x32b_x32(t_n + 32u, A1);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        m = fmaxf(m, fmaxf(__uint_as_float(B0[i]), __uint_as_float(B1[i])));
                 }
-                tcgen05_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&s_free[sb]);
             }
             const float mc = m * scale_log2e;
             float l = 0.f;
-            for (int j = 0; j < nkb; ++j, ++T, ++J) {   // pass 2: probabilities
-                const int sb = (int)(T % kSBuf);
-                const int pb = (int)(J & 1u);
-                mbar_wait(&s_full[sb], (T / kSBuf) & 1u);
-                tcgen05_fence_after();
-                const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
-                uint8_t* prow = sp + pb * 2 * kTile + (uint32_t)row * 128u;
-#pragma unroll 1
-                for (int c = 0; c < kBK; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32b_x32(t_s + (uint32_t)c, r);
-                    tmem_ld_wait();
+            {   // pass 2: probabilities; chunks of 32 keys ping-pong between RA and RB
+                uint32_t RA[32], RB[32];
+                // exp2, row sum, bf16 pack and the swizzled store of one 32-key chunk
+                auto emit = [&](const uint32_t* r, uint8_t* prow, int c) {
                     uint32_t pk[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
@@ -257,21 +270,49 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, float* __restrict__ lse, 
                         const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
                         pk[i] = *reinterpret_cast<const uint32_t*>(&h2);
                     }
-                    // the P V product that last read this P buffer must have finished
-                    if (c == 0 && J >= 2) mbar_wait(&p_free[pb], ((J >> 1) - 1u) & 1u);
                     uint8_t* box = prow + (c >> 6) * kTile;      // keys 0-63 | 64-127
                     const uint32_t ch0 = (uint32_t)(c & 63) >> 3;  // first 16-byte chunk: 0 or 4
 #pragma unroll
                     for (uint32_t q = 0; q < 4; ++q)
                         *reinterpret_cast<uint4*>(box + (((ch0 + q) ^ sw) << 4)) =
                             make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+                };
+                {
+                    const int sb = (int)(T % kSBuf);
+                    mbar_wait(&s_full[sb], (T / kSBuf) & 1u);
+                    tcgen05_fence_after();
+                    tmem_ld_32x32b_x32(tmem_base + (uint32_t)(sb * 128) + lane_sel, RA);
                 }
-                tcgen05_fence_before();
-                fence_async_smem();
-                __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(&s_free[sb]);
-                    mbar_arrive(&p_full[pb]);
+                for (int j = 0; j < nkb; ++j, ++T, ++J) {
+                    const int sb = (int)(T % kSBuf);
+                    const int pb = (int)(J & 1u);
+                    const uint32_t t_s = tmem_base + (uint32_t)(sb * 128) + lane_sel;
+                    uint8_t* prow = sp + pb * 2 * kTile + (uint32_t)row * 128u;
+                    tmem_ld_wait();                                  // RA: keys 0-31
+                    tmem_ld_32x32b_x32(t_s + 32u, RB);
+                    // the P V product that last read this P buffer must have finished
+                    if (J >= 2) mbar_wait(&p_free[pb], ((J >> 1) - 1u) & 1u);
+                    emit(RA, prow, 0);
+                    tmem_ld_wait();                                  // RB: keys 32-63
+                    tmem_ld_32x32b_x32(t_s + 64u, RA);
+                    emit(RB, prow, 32);
+                    tmem_ld_wait();                                  // RA: keys 64-95
+                    tmem_ld_32x32b_x32(t_s + 96u, RB);
+                    emit(RA, prow, 64);
+                    tmem_ld_wait();                                  // RB: every load of tile j is in
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&s_free[sb]);
+                    if (j + 1 < nkb) {
+                        const int sn = (int)((T + 1) % kSBuf);
+                        mbar_wait(&s_full[sn], ((T + 1) / kSBuf) & 1u);
+                        tcgen05_fence_after();
+                        tmem_ld_32x32b_x32(tmem_base + (uint32_t)(sn * 128) + lane_sel, RA);
+                    }
+                    emit(RB, prow, 96);
+                    fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&p_full[pb]);
                 }
             }
             // ---- O / l -> bf16 -> swizzled box -> TMA store; lse ----
@@ -345,6 +386,17 @@ constexpr int kBwdSmem = 2 * kTile /*K V*/ + 4 * kTile /*Q dO x2*/ + 2 * kTile /
                          2 * kTile /*dS^T*/ + 8 * 4096 /*staging*/ + 2 * 2 * 512 /*lse delta*/ +
                          256 + 1024;
 static_assert(kBwdSmem <= 227 * 1024, "shared memory budget of one CTA");
+
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+          "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]),
+          "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
 
 struct AttnBwdMaps {
     CUtensorMap qkv;    // [B*S, 3H] bf16, box {64, 128}: Q, K, V loads
@@ -531,34 +583,37 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
                 }
             }
         };
+        // lse (group 0) / delta (group 1) of the NEXT block are fetched while this block is worked
+        // on; S^T / dP^T come out of TMEM in chunks of 16 queries, one chunk in flight while the
+        // previous one is turned into P^T / dS^T (see the forward kernel).
+        float vnext = grp == 0 ? lse[vec0 + row] : delta[vec0 + row];
         for (int i = 0; i < nqb; ++i) {
             float* vec = svec + (i & 1) * 256;
-            if (grp == 0)
-                vec[row] = lse[vec0 + i * kBQ + row];
-            else
-                vec[128 + row] = delta[vec0 + i * kBQ + row];
+            vec[grp * 128 + row] = vnext;
             asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (i + 1 < nqb)
+                vnext = grp == 0 ? lse[vec0 + (i + 1) * kBQ + row] : delta[vec0 + (i + 1) * kBQ + row];
             {
                 const int h = grp;
-                mbar_wait(&st_full[h], (uint32_t)i & 1u);
-                tcgen05_fence_after();
                 if (i > 0) {
                     // block i-1 is finished on the tensor core: its dQ tile can leave, and the
-                    // P^T / dS^T boxes may be overwritten
+                    // P^T / dS^T boxes may be overwritten. (This wait comes BEFORE the one on
+                    // st_full: S^T of half 1 is issued behind block i-1's dQ product, so the
+                    // flush overlaps that MMA; the other order cost 15 us per call.)
                     mbar_wait(g2_done, (uint32_t)(i - 1) & 1u);
                     tcgen05_fence_after();
                     flush_f32(t_dq, head * kD, b * S + (i - 1) * kBQ + ew * 32);
                 }
-#pragma unroll 1
-                for (int c = 0; c < 64; c += 32) {
-                    const int qc = h * 64 + c;              // query column inside the block
-                    uint32_t rs[32], rd[32];
-                    tmem_ld_32x32b_x32(t_st + lane_sel + (uint32_t)qc, rs);
-                    tmem_ld_32x32b_x32(t_dpt + lane_sel + (uint32_t)qc, rd);
-                    tmem_ld_wait();
-                    uint32_t pk[16], dk[16];
+                mbar_wait(&st_full[h], (uint32_t)i & 1u);
+                tcgen05_fence_after();
+                const uint32_t boff = (uint32_t)h * kTile;
+                uint32_t sa[16], da[16], sb2[16], db2[16];
+                // P^T and dS^T of 16 queries: exp2, the dS product, bf16 pack, swizzled stores
+                auto emit = [&](const uint32_t* rs, const uint32_t* rd, int c) {
+                    const int qc = h * 64 + c;
+                    uint32_t pk[8], dk[8];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) {
+                    for (int k = 0; k < 8; ++k) {
                         const float2 l2 = *reinterpret_cast<const float2*>(vec + qc + 2 * k);
                         const float2 d2 = *reinterpret_cast<const float2*>(vec + 128 + qc + 2 * k);
                         const float p0 = ex2_approx(fmaf(__uint_as_float(rs[2 * k]), scale_log2e, -l2.x));
@@ -570,24 +625,41 @@ attn_bwd_kernel(const __grid_constant__ AttnBwdMaps maps, const float* __restric
                         pk[k] = *reinterpret_cast<const uint32_t*>(&ph);
                         dk[k] = *reinterpret_cast<const uint32_t*>(&dh);
                     }
-                    const uint32_t boff = (uint32_t)h * kTile;
                     const uint32_t ch0 = (uint32_t)c >> 3;
 #pragma unroll
-                    for (uint32_t q = 0; q < 4; ++q) {
+                    for (uint32_t q = 0; q < 2; ++q) {
                         const uint32_t off = boff + (((ch0 + q) ^ sw) << 4);
                         *reinterpret_cast<uint4*>(ptrow + off) =
                             make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
                         *reinterpret_cast<uint4*>(dstrow + off) =
                             make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
                     }
-                }
+                };
+                const uint32_t a_st = t_st + lane_sel + (uint32_t)(h * 64);
+                const uint32_t a_dp = t_dpt + lane_sel + (uint32_t)(h * 64);
+                tmem_ld_32x32b_x16(a_st, sa);
+                tmem_ld_32x32b_x16(a_dp, da);
+                tmem_ld_wait();
+                tmem_ld_32x32b_x16(a_st + 16u, sb2);
+                tmem_ld_32x32b_x16(a_dp + 16u, db2);
+                emit(sa, da, 0);
+                tmem_ld_wait();
+                tmem_ld_32x32b_x16(a_st + 32u, sa);
+                tmem_ld_32x32b_x16(a_dp + 32u, da);
+                emit(sb2, db2, 16);
+                tmem_ld_wait();
+                tmem_ld_32x32b_x16(a_st + 48u, sb2);
+                tmem_ld_32x32b_x16(a_dp + 48u, db2);
+                emit(sa, da, 32);
+                tmem_ld_wait();
+                // every load of this half is in: the tensor core may overwrite S^T / dP^T
                 tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&st_free[h]);
+                emit(sb2, db2, 48);
                 fence_async_smem();
                 __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(&st_free[h]);
-                    mbar_arrive(&pt_full[h]);
-                }
+                if (lane == 0) mbar_arrive(&pt_full[h]);
             }
         }
         mbar_wait(g2_done, (uint32_t)(nqb - 1) & 1u);
@@ -766,6 +838,8 @@ TFOP_API int tfop_attn_fwd(const void* qkv, void* out, float* lse, int B, int S,
 // i.e. it IS the gradient of the packed projection output. `out` and `lse` are the forward's
 // results. Scratch (caller-provided, so the call allocates nothing): delta[B, heads, S] fp32 and
 // dq32[B*S, H] fp32; dq32 is zeroed here and holds the unrounded dQ afterwards.
+// (Letting the rounding kernel hand dq32 back zeroed instead of clearing it here was tried: its
+// zero stores made that kernel 27 us slower to save a 7 us memset.)
 TFOP_API int tfop_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
                            void* dqkv, float* delta, float* dq32, int B, int S, int heads,
                            int head_dim, cudaStream_t stream) {
