@@ -43,6 +43,20 @@ def main():
     y = add_bias_layernorm(h, bias, res, g, b, 1e-12)
     dy = torch.randn_like(y)
     out["ln_bwd_us"] = timed(lambda: torch.autograd.grad(y, (h, bias, res, g, b), dy, retain_graph=True), iters)
+    # the backward kernel alone (no allocations, no clears), two and four rows per thread and trip
+    from tf_operator_b200.ops import _lib
+    lib = _lib.load()
+    s_in = (h + bias + res).detach()
+    mean = s_in.float().mean(1)
+    rstd = (s_in.float().var(1, unbiased=False) + 1e-12).rsqrt()
+    dx = torch.empty_like(s_in)
+    dg, db_, dbi = (torch.zeros(H, device=dev) for _ in range(3))
+    for r in (2, 4):
+        lib.tfop_ln_set_bwd_rows(r)
+        out[f"ln_bwd_kernel_only_rows{r}_us"] = timed(lambda: lib.tfop_ln_bwd(
+            dy.data_ptr(), s_in.data_ptr(), mean.data_ptr(), rstd.data_ptr(), g.data_ptr(), dx.data_ptr(),
+            dg.data_ptr(), db_.data_ptr(), dbi.data_ptr(), rows, H, _lib.stream_handle()), iters)
+    lib.tfop_ln_set_bwd_rows(2)
     x = torch.randn(rows, I, device=dev).bfloat16().requires_grad_(True)
     bi = torch.randn(I, device=dev).bfloat16().requires_grad_(True)
     out["bias_gelu_fwd_us"] = timed(lambda: bias_gelu(x, bi), iters)

@@ -232,7 +232,7 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 // whole row plus 3 row-length accumulators: 224 registers, 8 warps per SM, 1.1 TB/s). Row sums
 // go warp shuffle -> shared memory -> every thread of the row lane; two barriers per trip.
 template <int R>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, R <= 2 ? 3 : 2)
 ln_bwd_tiled_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ s,
                     const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                     const __nv_bfloat16* __restrict__ gamma, __nv_bfloat16* __restrict__ dx,
@@ -471,6 +471,13 @@ int launch_bwd(const void* dy, const void* s, const float* mean, const float* rs
 
 }  // namespace
 
+static int g_ln_bwd_rows = 2;
+// Benchmark hook: rows per thread and trip of the tiled LayerNorm backward (2 or 4).
+TFOP_API int tfop_ln_set_bwd_rows(int r) {
+    TFOP_REQUIRE(r == 2 || r == 4, "rows per trip: 2 or 4");
+    g_ln_bwd_rows = r;
+    return 0;
+}
 static int g_ln_force_warp_rows = 0;
 // Test hook: 1 routes every LayerNorm backward through the warp-per-row kernel.
 TFOP_API int tfop_ln_force_warp_rows(int on) {
@@ -508,13 +515,22 @@ TFOP_API int tfop_ln_bwd(const void* dy, const void* s, const float* mean, const
                  "layernorm: hidden must be a multiple of 8 and <= 1536");
     TFOP_REQUIRE(dgamma != nullptr && dbeta != nullptr, "layernorm bwd needs dgamma and dbeta");
     if (H % 256 == 0 && !g_ln_force_warp_rows) {
-        constexpr int R = 4;
+        // R rows per thread and trip. ncu on R = 4 (128 registers, 2 blocks = 16 warps per SM):
+        // 1.2 TB/s, long-scoreboard stalls dominate, issue slots 38 % busy - latency-bound for
+        // lack of warps. R = 2 fits three blocks per SM (tfop_ln_set_bwd_rows switches, for A/B).
+        const int R = g_ln_bwd_rows;
         const int rows_per_trip = (256 / (H / 8)) * R;
         int grid = (rows + rows_per_trip - 1) / rows_per_trip;
-        if (grid > 148 * 2) grid = 148 * 2;
-        ln_bwd_tiled_kernel<R><<<grid, 256, 0, stream>>>(
-            (const __nv_bfloat16*)dy, (const __nv_bfloat16*)s, mean, rstd,
-            (const __nv_bfloat16*)gamma, (__nv_bfloat16*)dx, dgamma, dbeta, dbias, rows, H);
+        const int per_sm = R <= 2 ? 3 : 2;
+        if (grid > 148 * per_sm) grid = 148 * per_sm;
+        if (R <= 2)
+            ln_bwd_tiled_kernel<2><<<grid, 256, 0, stream>>>(
+                (const __nv_bfloat16*)dy, (const __nv_bfloat16*)s, mean, rstd,
+                (const __nv_bfloat16*)gamma, (__nv_bfloat16*)dx, dgamma, dbeta, dbias, rows, H);
+        else
+            ln_bwd_tiled_kernel<4><<<grid, 256, 0, stream>>>(
+                (const __nv_bfloat16*)dy, (const __nv_bfloat16*)s, mean, rstd,
+                (const __nv_bfloat16*)gamma, (__nv_bfloat16*)dx, dgamma, dbeta, dbias, rows, H);
         TFOP_CUDA(cudaGetLastError());
         return 0;
     }

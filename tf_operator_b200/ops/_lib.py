@@ -118,6 +118,7 @@ _SIGS = {
     "tfop_ln_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "tfop_ln_force_warp_rows": (c_int, [c_int]),
+    "tfop_ln_set_bwd_rows": (c_int, [c_int]),
     "tfop_bias_gelu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "tfop_bias_act_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                   c_int, c_void_p]),
