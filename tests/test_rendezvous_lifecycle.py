@@ -178,3 +178,44 @@ def test_deleting_the_job_object_clears_its_rendezvous_state():
         # a second job of the same name gets a different uid -> a different scope
         again = c.store.create("pytorchjobs", job)
         assert again["metadata"]["uid"] != uid
+
+
+def test_a_wait_inside_a_generation_ends_when_the_generation_does(srv):
+    """Seen on 8 GPUs: rank A gets through join of generation g a moment before a late restart of
+    rank B supersedes g. A then waits for B's handle under g - a key nobody will ever publish (the
+    generation's keys are dropped) - while everyone else waits for A in g+1; all time out. A wait
+    that names its generation raises Superseded at once, and A re-joins."""
+    from tf_operator_b200.launcher.rendezvous import Superseded
+    scope = "ns/job/uid-9/comm0"
+    a, b = RendezvousClient(srv.addr), RendezvousClient(srv.addr)
+    assert _run([lambda: a.join(scope, 0, 2), lambda: b.join(scope, 1, 2)]) == [0, 0]
+    got = {}
+
+    def waits(kind):
+        t0 = time.time()
+        try:
+            if kind == "get":
+                a.get(f"{scope}/g0/ipc/1", timeout=30, scope=scope, gen=0)
+            elif kind == "barrier":
+                RendezvousClient(srv.addr).barrier(f"{scope}/g0/ready", 2, timeout=30, scope=scope, gen=0)
+            else:
+                RendezvousClient(srv.addr, uds_path=srv.uds_path).fd_get(
+                    f"{scope}/g0/nvls/fd", timeout=30, scope=scope, gen=0)
+            got[kind] = "returned"
+        except Superseded:
+            got[kind] = time.time() - t0
+    ts = [threading.Thread(target=waits, args=(k,)) for k in ("get", "barrier", "fd")]
+    [t.start() for t in ts]
+    time.sleep(0.3)
+    assert not got                                    # all three are blocked
+    b2 = RendezvousClient(srv.addr)                   # rank 1 restarted: a new identity
+    j = threading.Thread(target=lambda: got.setdefault("b2", b2.join(scope, 1, 2, timeout=20)))
+    j.start()
+    [t.join(10) for t in ts]
+    assert all(isinstance(got.get(k), float) and got[k] < 5 for k in ("get", "barrier", "fd")), got
+    # A goes back to join and the two meet in generation 1; an unscoped wait keeps its old meaning
+    assert a.join(scope, 0, 2, timeout=20) == 1
+    j.join(10)
+    assert got["b2"] == 1
+    with pytest.raises(TimeoutError):
+        a.get(f"{scope}/g1/never", timeout=0.3)

@@ -22,7 +22,8 @@ re-creates a whole job under the same name):
 
 Wire protocol (TCP and the Unix socket alike): one JSON object per line, values base64.
   {"op":"set","key":k,"value":b64} -> {"ok":true}
-  {"op":"get","key":k,"timeout":s} -> {"ok":true,"value":b64} | {"ok":false,"error":"timeout"}
+  {"op":"get","key":k,"timeout":s[,"scope":s,"gen":g]} -> {"ok":true,"value":b64} |
+                                      {"ok":false,"error":"timeout"|"superseded"}
   {"op":"add","key":k,"delta":n}   -> {"ok":true,"value":n}
   {"op":"join","scope":s,"rank":r,"world":w,"timeout":t} -> {"ok":true,"value":generation}
   {"op":"delete_prefix","prefix":p}-> {"ok":true,"value":count}
@@ -105,14 +106,21 @@ class RendezvousServer:
         return f"{self.host}:{self.port}"
 
     # ------------------------------------------------------------------ operations
-    def _wait_key(self, key: str, timeout: float, store) -> bool:
+    def _wait_key(self, key: str, timeout: float, store, scope: str = "", gen: int = -1) -> str:
+        """"" when the key is there, "timeout", or "superseded": the waiter named the rendezvous
+        generation it belongs to (scope, gen) and that generation is over - a peer restarted, its
+        keys are gone and nobody will ever publish the one waited for."""
         end = time.time() + timeout
         while key not in store:
+            if scope:
+                st = self._scopes.get(scope)
+                if st is None or st.gen != gen:
+                    return "superseded"
             left = end - time.time()
             if left <= 0:
-                return False
+                return "timeout"
             self._cv.wait(left)
-        return True
+        return ""
 
     def _dispatch(self, req):
         op = req.get("op")
@@ -123,8 +131,10 @@ class RendezvousServer:
             return {"ok": True}
         if op == "get":
             with self._cv:
-                if not self._wait_key(req["key"], float(req.get("timeout", 60)), self._data):
-                    return {"ok": False, "error": "timeout"}
+                err = self._wait_key(req["key"], float(req.get("timeout", 60)), self._data,
+                                     str(req.get("scope", "")), int(req.get("gen", -1)))
+                if err:
+                    return {"ok": False, "error": err}
                 return {"ok": True, "value": base64.b64encode(self._data[req["key"]]).decode()}
         if op == "add":
             with self._cv:
@@ -233,15 +243,16 @@ class RendezvousServer:
                         conn.sendall(b'{"ok": true}\n')
                     elif op == "fd_get":
                         with self._cv:
-                            ok = self._wait_key(req["key"], float(req.get("timeout", 60)), self._fds)
-                            fd = os.dup(self._fds[req["key"]]) if ok else -1
-                        if ok:
+                            err = self._wait_key(req["key"], float(req.get("timeout", 60)), self._fds,
+                                                 str(req.get("scope", "")), int(req.get("gen", -1)))
+                            fd = os.dup(self._fds[req["key"]]) if not err else -1
+                        if not err:
                             try:
                                 socket.send_fds(conn, [b'{"ok": true}\n'], [fd])
                             finally:
                                 os.close(fd)
                         else:
-                            conn.sendall(b'{"ok": false, "error": "timeout"}\n')
+                            conn.sendall((json.dumps({"ok": False, "error": err}) + "\n").encode())
                     else:
                         for fd in fds:
                             os.close(fd)
@@ -316,9 +327,14 @@ class RendezvousClient:
     def set(self, key: str, value: bytes) -> None:
         self._call({"op": "set", "key": key, "value": base64.b64encode(value).decode()})
 
-    def get(self, key: str, timeout: Optional[float] = None) -> bytes:
-        return base64.b64decode(self._call({"op": "get", "key": key,
-                                            "timeout": timeout or self.timeout}))
+    def get(self, key: str, timeout: Optional[float] = None, scope: str = "", gen: int = -1) -> bytes:
+        """Blocks until the key is there. With ``scope`` / ``gen`` (the rendezvous generation the
+        caller joined) it raises ``Superseded`` as soon as that generation is over instead of
+        waiting out the timeout for a key that will never come."""
+        req = {"op": "get", "key": key, "timeout": timeout or self.timeout}
+        if scope:
+            req.update(scope=scope, gen=gen)
+        return base64.b64decode(self._call(req))
 
     def add(self, key: str, delta: int = 1) -> int:
         return int(self._call({"op": "add", "key": key, "delta": delta}))
@@ -348,17 +364,19 @@ class RendezvousClient:
                     raise TimeoutError("rendezvous join kept being superseded")
 
     def all_gather(self, prefix: str, rank: int, world: int, value: bytes,
-                   timeout: Optional[float] = None) -> List[bytes]:
-        """Every rank publishes ``value``; returns all ranks' values in rank order."""
+                   timeout: Optional[float] = None, scope: str = "", gen: int = -1) -> List[bytes]:
+        """Every rank publishes ``value``; returns all ranks' values in rank order. ``scope`` /
+        ``gen``: see ``get``."""
         self.set(f"{prefix}/{rank}", value)
-        return [self.get(f"{prefix}/{r}", timeout) for r in range(world)]
+        return [self.get(f"{prefix}/{r}", timeout, scope, gen) for r in range(world)]
 
-    def barrier(self, prefix: str, world: int, timeout: Optional[float] = None) -> None:
+    def barrier(self, prefix: str, world: int, timeout: Optional[float] = None, scope: str = "",
+                gen: int = -1) -> None:
         n = self.add(f"{prefix}/count", 1)
-        gen = (n - 1) // world          # reusable: generation = arrivals // world
+        round_ = (n - 1) // world       # reusable: round = arrivals // world
         if n % world == 0:
-            self.set(f"{prefix}/gen/{gen}", b"1")
-        self.get(f"{prefix}/gen/{gen}", timeout)
+            self.set(f"{prefix}/gen/{round_}", b"1")
+        self.get(f"{prefix}/gen/{round_}", timeout, scope, gen)
 
     # ---- descriptors over the Unix socket --------------------------------------------------
     def _uds(self) -> socket.socket:
@@ -375,12 +393,14 @@ class RendezvousClient:
             socket.send_fds(s, [json.dumps({"op": "fd_put", "key": key}).encode()], [fd])
             self._check(json.loads(s.makefile("rb").readline()))
 
-    def fd_get(self, key: str, timeout: Optional[float] = None) -> int:
-        """Receive a duplicate of the descriptor stored under ``key`` (blocks until it is there).
-        The caller owns the returned descriptor."""
+    def fd_get(self, key: str, timeout: Optional[float] = None, scope: str = "", gen: int = -1) -> int:
+        """Receive a duplicate of the descriptor stored under ``key`` (blocks until it is there;
+        ``scope`` / ``gen`` as in ``get``). The caller owns the returned descriptor."""
         with self._uds() as s:
-            s.sendall(json.dumps({"op": "fd_get", "key": key,
-                                  "timeout": timeout or self.timeout}).encode())
+            req = {"op": "fd_get", "key": key, "timeout": timeout or self.timeout}
+            if scope:
+                req.update(scope=scope, gen=gen)
+            s.sendall(json.dumps(req).encode())
             msg, fds, _, _ = socket.recv_fds(s, 65536, 1)
             try:
                 self._check(json.loads(msg))

@@ -136,14 +136,14 @@ class ReplicaContext:
         additionally binds a multicast (NVLS) buffer of that size when the box supports it
         (``comm.nvls_bytes`` is 0 otherwise); under the launcher the multicast descriptor goes
         through its broker too, so no torch.distributed group is created."""
-        comm = self._symmetric_comm(nbytes, tag)
-        comm.nvls_bytes = 0
-        if nvls_bytes and self.world_size > 1:
-            if getattr(comm, "_rdv", None) is None:
+        comm = self._symmetric_comm(nbytes, tag, nvls_bytes)
+        if getattr(comm, "_rdv", None) is None:
+            comm.nvls_bytes = 0
+            if nvls_bytes and self.world_size > 1:
                 import torch.distributed as dist
                 if not dist.is_initialized():
                     self.init_process_group("gloo")
-            comm.enable_nvls(nvls_bytes)
+                comm.enable_nvls(nvls_bytes)
         return comm
 
     def rendezvous_scope(self, tag: str) -> str:
@@ -151,15 +151,20 @@ class ReplicaContext:
         keeps a re-created job of the same name away from its predecessor's keys."""
         return f"{self.namespace}/{self.job_name}/{self.raw.get('TFOP_JOB_UID', '')}/{tag}"
 
-    def _symmetric_comm(self, nbytes: int, tag: str):
+    def _symmetric_comm(self, nbytes: int, tag: str, nvls_bytes: int = 0):
         from .symm import SymmetricComm
         addr = self.raw.get("TFOP_RENDEZVOUS")
         if addr and self.world_size > 1:
+            # IPC handles AND the multicast buffer are set up inside one rendezvous generation
             return rendezvous_comm(addr, self.raw.get("TFOP_RENDEZVOUS_UDS", ""),
-                                   self.rendezvous_scope(tag), self.rank, self.world_size, nbytes)
+                                   self.rendezvous_scope(tag), self.rank, self.world_size, nbytes,
+                                   nvls_bytes=nvls_bytes)
         if self.world_size > 1:
             return SymmetricComm.from_torch_distributed(nbytes)
         return SymmetricComm.create(0, 1, nbytes, lambda b: [b])
+
+
+_ABANDONED: list = []      # communicators of superseded generations (see rendezvous_comm)
 
 
 def rendezvous_comm(addr: str, uds_path: str, scope: str, rank: int, world: int, nbytes: int,
@@ -171,16 +176,34 @@ def rendezvous_comm(addr: str, uds_path: str, scope: str, rank: int, world: int,
     keeps the client for the NVLS descriptor hand-off and for its exit barrier."""
     from ..launcher.rendezvous import RendezvousClient
     from .symm import SymmetricComm
+    import time
+    from ..launcher.rendezvous import Superseded
     cli = RendezvousClient(addr, uds_path=uds_path)
-    gen = cli.join(scope, rank, world)
-    prefix = f"{scope}/g{gen}"
-    comm = SymmetricComm.create(rank, world, nbytes,
-                                lambda b: cli.all_gather(prefix + "/ipc", rank, world, b))
-    cli.barrier(prefix + "/ready", world)
-    comm._rdv = (cli, prefix)
+    deadline = time.time() + cli.timeout
+    while True:
+        gen = cli.join(scope, rank, world, timeout=max(1.0, deadline - time.time()))
+        prefix = f"{scope}/g{gen}"
+        comm = None
+        try:
+            # every wait names its generation: if a peer restarts while the handles are being
+            # exchanged, the generation is over and this rank goes back to join the next one
+            # (seen on 8 GPUs: one rank got through join just before a late restart superseded
+            # the generation, waited for handles nobody would publish, and everyone timed out)
+            comm = SymmetricComm.create(
+                rank, world, nbytes,
+                lambda b: cli.all_gather(prefix + "/ipc", rank, world, b, scope=scope, gen=gen))
+            cli.barrier(prefix + "/ready", world, scope=scope, gen=gen)
+            comm._rdv = (cli, prefix)
+            comm._rdv_gen = (scope, gen)
+            comm.nvls_bytes = 0
+            if nvls_bytes:
+                comm.enable_nvls(nvls_bytes)
+            break
+        except Superseded:
+            if comm is not None:
+                _ABANDONED.append(comm)      # peers may have mapped it: kept until process exit
+            if time.time() >= deadline:
+                raise TimeoutError("rendezvous kept being superseded while exchanging handles")
     comm.generation = gen
     comm._exit_barrier = lambda: cli.barrier(prefix + "/exit", world, timeout=60)
-    comm.nvls_bytes = 0
-    if nvls_bytes:
-        comm.enable_nvls(nvls_bytes)
     return comm

@@ -27,6 +27,9 @@ AUTO, ONE_SHOT, TWO_SHOT = 0, 1, 2
 RETRYABLE_EXIT_CODE = 138
 
 
+_ORPHANS: list = []       # handles of communicators whose formation was interrupted
+
+
 class CommError(RuntimeError):
     """A cross-rank barrier of a collective timed out: a peer is dead or wedged. The collective
     was abandoned (no data was reduced or stored); the replica should exit with
@@ -72,7 +75,12 @@ class SymmetricComm:
             hb = lib.tfop_comm_handle_bytes()
             mine = C.create_string_buffer(hb)
             _lib.check(lib.tfop_comm_get_handle(h, mine), "comm_get_handle")
-            allh = exchange(mine.raw)
+            try:
+                allh = exchange(mine.raw)
+            except BaseException:
+                # a peer may already hold this handle: the allocation stays until process exit
+                _ORPHANS.append(h)
+                raise
             assert len(allh) == world and all(len(b) == hb for b in allh)
             blob = C.create_string_buffer(b"".join(allh), hb * world)
             if world > 1:
@@ -213,6 +221,9 @@ class SymmetricComm:
     def _enable_nvls_brokered(self, nbytes: int) -> bool:
         import os
         cli, prefix = self._rdv
+        # every wait names the rendezvous generation this communicator belongs to: a peer that
+        # restarts in the middle ends the wait with Superseded instead of a timeout
+        sg = dict(zip(("scope", "gen"), getattr(self, "_rdv_gen", ("", -1))))
         self.nvls_bytes = 0
         if self.world == 1:
             return False
@@ -228,22 +239,22 @@ class SymmetricComm:
                     ok = False
                 cli.set(f"{base}/created", b"1" if ok else b"0")
             else:
-                if cli.get(f"{base}/created") != b"1":
+                if cli.get(f"{base}/created", **sg) != b"1":
                     ok = False
                 elif ok:
-                    fd = cli.fd_get(f"{base}/fd")
+                    fd = cli.fd_get(f"{base}/fd", **sg)
                     try:
                         ok = lib.tfop_nvls_import(self._h, nbytes, fd) == 0
                     finally:
                         os.close(fd)
             # every rank must have the object before any binds; all or nothing
-            votes = cli.all_gather(f"{base}/ok", self.rank, self.world, b"1" if ok else b"0")
+            votes = cli.all_gather(f"{base}/ok", self.rank, self.world, b"1" if ok else b"0", **sg)
             if any(v != b"1" for v in votes):
                 return False
             _lib.check(lib.tfop_nvls_add_device(self._h), "nvls_add_device")
-            cli.barrier(f"{base}/added", self.world)
+            cli.barrier(f"{base}/added", self.world, **sg)
             _lib.check(lib.tfop_nvls_bind(self._h), "nvls_bind")
-            cli.barrier(f"{base}/bound", self.world)
+            cli.barrier(f"{base}/bound", self.world, **sg)
         self.nvls_bytes = lib.tfop_nvls_bytes(self._h)
         return True
 
