@@ -219,3 +219,66 @@ def test_a_wait_inside_a_generation_ends_when_the_generation_does(srv):
     assert got["b2"] == 1
     with pytest.raises(TimeoutError):
         a.get(f"{scope}/g1/never", timeout=0.3)
+
+
+class _FakeComm:
+    """Stands in for runtime.symm.SymmetricComm on a CPU box: records what rendezvous_comm does."""
+    made = []
+
+    def __init__(self, rank, world, handles):
+        self.rank, self.world, self.handles = rank, world, handles
+        self.nvls_bytes = -1
+        self.nvls_calls = []
+        _FakeComm.made.append(self)
+
+    @classmethod
+    def create(cls, rank, world, nbytes, exchange, device=None):
+        return cls(rank, world, exchange(f"h{rank}-{nbytes}".encode()))
+
+    def enable_nvls(self, nbytes):
+        cli, prefix = self._rdv
+        scope, gen = self._rdv_gen
+        self.nvls_calls.append((prefix, scope, gen))
+        cli.barrier(prefix + "/nvls/bound", self.world, scope=scope, gen=gen)
+        self.nvls_bytes = nbytes
+        return True
+
+
+def test_rendezvous_comm_forms_ipc_and_nvls_in_one_generation_and_rejoins_when_superseded(srv, monkeypatch):
+    """runtime.env.rendezvous_comm with the communicator faked: the handles and the multicast
+    set-up happen under <scope>/g<gen>/ with every wait naming (scope, gen); a restart of a peer
+    in the middle sends the survivor back to join, and both end up in the next generation."""
+    import tf_operator_b200.runtime.symm as symm
+    from tf_operator_b200.runtime.env import _ABANDONED, rendezvous_comm
+    monkeypatch.setattr(symm, "SymmetricComm", _FakeComm)
+    _FakeComm.made.clear()
+    scope = "ns/job/uid-7/comm0"
+    comms = _run([lambda r=r: rendezvous_comm(srv.addr, srv.uds_path, scope, r, 2, 1 << 20, nvls_bytes=4096)
+                  for r in range(2)])
+    for r, c in enumerate(comms):
+        assert c.generation == 0 and c.handles == [b"h0-1048576", b"h1-1048576"]
+        assert c._rdv[1] == f"{scope}/g0" and c._rdv_gen == (scope, 0) and c.nvls_bytes == 4096
+        assert c.nvls_calls == [(f"{scope}/g0", scope, 0)]
+    _run([c._exit_barrier for c in comms])             # the exit barrier of the generation works
+    # rank 1 dies and comes back while rank 0 (restarted too) is already exchanging handles in
+    # generation 1 with ... nobody: it is alone there until the second restart of rank 1 opens
+    # generation 2; its wait ends with Superseded inside rendezvous_comm and it follows
+    n_before = len(_ABANDONED)
+    res = {}
+    t0 = threading.Thread(target=lambda: res.setdefault(0, rendezvous_comm(
+        srv.addr, srv.uds_path, scope, 0, 2, 1 << 20, nvls_bytes=4096)))
+    t0.start()                                          # new identity for rank 0 -> generation 1
+    time.sleep(0.3)
+    first = RendezvousClient(srv.addr)                  # rank 1's first restart joins generation 1 ...
+    assert first.join(scope, 1, 2, timeout=10) == 1
+    time.sleep(0.3)                                     # ... rank 0 is now past join, waiting for h1
+    first.close()                                       # ... and dies before publishing its handle
+    t1 = threading.Thread(target=lambda: res.setdefault(1, rendezvous_comm(
+        srv.addr, srv.uds_path, scope, 1, 2, 1 << 20, nvls_bytes=4096)))
+    t1.start()                                          # second restart of rank 1 -> generation 2
+    t0.join(20)
+    t1.join(20)
+    assert res[0].generation == 2 and res[1].generation == 2
+    assert res[0].handles == res[1].handles == [b"h0-1048576", b"h1-1048576"]
+    assert res[0].nvls_bytes == 4096 and res[0]._rdv_gen == (scope, 2)
+    assert len(_ABANDONED) == n_before                  # create() itself was interrupted: nothing to keep
