@@ -42,7 +42,9 @@ def _recv(sock: socket.socket):
         if not chunk:
             raise ConnectionError("peer closed")
         data += chunk
-    return torch.load(io.BytesIO(bytes(data)), weights_only=False)
+    # weights_only: the port is reachable by any local process; the payloads are plain
+    # containers of tensors, numbers and strings, so the restricted unpickler is enough
+    return torch.load(io.BytesIO(bytes(data)), weights_only=True)
 
 
 class ParameterServer:
