@@ -230,6 +230,7 @@ int tfop_ln_bwd(const void* dy, const void* s, const float* mean, const float* r
 /* Test hook: 1 routes every LayerNorm backward through the warp-per-row kernel (the default for
  * H % 256 == 0 is the tiled kernel: H/8 threads per row, 4 rows per thread and trip). */
 int tfop_ln_force_warp_rows(int on);
+int tfop_ln_set_bwd_rows(int rows);   /* rows per thread and trip of the tiled backward: 2 (default) or 4 */
 int tfop_bias_gelu_fwd(const void* h, const void* bias, void* y, int rows, int H,
                        cudaStream_t stream);
 int tfop_bias_act_bwd(const void* dy, const void* h, const void* bias, void* dh, float* dbias,
@@ -302,11 +303,22 @@ int tfop_gemm_allreduce_set_timeout(long long cycles);
 int tfop_gemm_allreduce_bf16_tn(tfop_comm* c, const void* A, const void* B, int M, int N, int K,
                                 int lda, int ldb, int ldo, float scale, size_t ws_off,
                                 size_t out_off, int max_ctas, cudaStream_t stream);
-/* NVLS flavour: out region in the multicast-bound buffer, partials stay local, the NVSwitch
- * reduces and broadcasts. ws_off: (tiles_per_owner + 2) * 4 zeroed bytes in the IPC buffer. */
+/* NVLS flavour: out region in the multicast-bound buffer, partials stay local (stored by the
+ * cta_group::2 GEMM's TMA epilogue), reducer warps in the same kernel let the NVSwitch reduce and
+ * broadcast the tiles as they complete. a_mn / b_mn as in tfop_gemm_bf16 ((1,1) = dY^T X from the
+ * stored activations). ws_off: tfop_gemm_allreduce_nvls_workspace_bytes(M, N, world) zeroed bytes
+ * of counters in the IPC buffer, tied to one (M, N, world) and one tile width. N, ldo: multiples
+ * of 8. _tn = both operands K-major. Hooks: tile width 0 (heuristic) / 128 / 256; legacy = 1 runs
+ * the first-generation kernel (one CTA per tile, three stages, K-major operands only). */
+size_t tfop_gemm_allreduce_nvls_workspace_bytes(int M, int N, int world);
+int tfop_gemm_allreduce_nvls_bf16(tfop_comm* c, const void* A, const void* B, int M, int N, int K,
+                                  int lda, int ldb, int ldo, int a_mn, int b_mn, float scale,
+                                  size_t ws_off, size_t out_off, int max_ctas, cudaStream_t stream);
 int tfop_gemm_allreduce_nvls_bf16_tn(tfop_comm* c, const void* A, const void* B, int M, int N,
                                      int K, int lda, int ldb, int ldo, float scale, size_t ws_off,
                                      size_t out_off, int max_ctas, cudaStream_t stream);
+int tfop_gemm_allreduce_set_tile_n(int tile_n);
+int tfop_gemm_allreduce_set_legacy(int on);
 int tfop_gemm_allreduce_emulated(tfop_comm** comms, int world, const void* const* As,
                                  const void* const* Bs, int M, int N, int K, int lda, int ldb,
                                  int ldo, float scale, size_t ws_off, size_t out_off,
