@@ -391,3 +391,38 @@ def test_mxjob_kvstore_training(cluster):
     log = cli.get_logs(name, master=False, replica_type="worker")[f"{name}-worker-0"]
     assert "DMLC_ROLE=worker servers=1 workers=1 root=mxnet-job-scheduler-0:9091" in log and "final loss" in log
     wait(lambda: set(phases(cluster, name)) == {f"{name}-worker-0"})     # cleanPodPolicy Running
+
+
+# replica_restart_policy_tests.py:27-156 with the data-plane life cycle of the GPU job, on CPU -------
+@pytest.mark.parametrize("world", [2, 8])
+def test_killed_replica_reforms_the_gang_control_plane_version(world, tmp_path):
+    """The kill-and-restart cycle of tests/test_multigpu_gpu.py with the GPU parts faked
+    (tests/workers/fake_ddp.py): rank 1 is SIGKILLed at step 25 (exit 137, retryable), its peers
+    lose it, exit 138, the operator re-creates every replica, the gang re-forms in a later
+    rendezvous generation - whatever order the restarts arrive in - and resumes from step 20."""
+    cl = LocalCluster(topology=synthetic(world), serve_http=False,
+                      kubelet_options=KubeletOptions(cwd=REPO, restart_backoff=0.05,
+                                                     gpus_per_replica_default=1))
+    try:
+        ckpt, marker, res = tmp_path / "ckpt.json", tmp_path / "killed", tmp_path / "result.json"
+        cmd = ["python", os.path.join(REPO, "tests", "workers", "fake_ddp.py"), "40", str(ckpt), str(res), "2.0"]
+
+        def spec(n):
+            ctr = {"name": "pytorch", "image": "test:local", "command": cmd,
+                   "env": [{"name": "TFOP_FAULT_INJECT", "value": f"1:25:{marker}"}]}
+            return {"replicas": n, "restartPolicy": "ExitCode", "template": {"spec": {"containers": [ctr]}}}
+        job = {"apiVersion": "kubeflow.org/v1", "kind": "PyTorchJob",
+               "metadata": {"name": "fake-restart", "namespace": "default"},
+               "spec": {"runPolicy": {"cleanPodPolicy": "None"},
+                        "pytorchReplicaSpecs": {"Master": spec(1), "Worker": spec(world - 1)}}}
+        cli = PyTorchJobClient(cluster=cl)
+        cli.create(job)
+        cli.wait_for_job("fake-restart", polling_interval=0.05, timeout_seconds=120)
+        logs = cli.get_logs("fake-restart", master=False)
+        dump = "\n".join(f"--- {k}\n{v[-1500:]}" for k, v in logs.items())
+        assert cli.is_job_succeeded("fake-restart"), dump
+        assert marker.exists()
+        out = json.load(open(res))
+        assert out["world"] == world and out["generation"] >= 1 and out["resumed_from"] == 20, out
+    finally:
+        cl.stop()
