@@ -409,7 +409,8 @@ def test_killed_replica_reforms_the_gang_control_plane_version(world, tmp_path):
 
         def spec(n):
             ctr = {"name": "pytorch", "image": "test:local", "command": cmd,
-                   "env": [{"name": "TFOP_FAULT_INJECT", "value": f"1:25:{marker}"}]}
+                   "env": [{"name": "TFOP_FAULT_INJECT", "value": f"1:25:{marker}"},
+                           {"name": "FAKE_START_JITTER_S", "value": os.environ.get("FAKE_START_JITTER_S", "0.5")}]}
             return {"replicas": n, "restartPolicy": "ExitCode", "template": {"spec": {"containers": [ctr]}}}
         job = {"apiVersion": "kubeflow.org/v1", "kind": "PyTorchJob",
                "metadata": {"name": "fake-restart", "namespace": "default"},

@@ -38,6 +38,11 @@ def main():
     step_timeout = float(sys.argv[4]) if len(sys.argv) > 4 else 2.0
     symm.SymmetricComm = FakeComm
     ctx = ReplicaContext.from_env()
+    jitter = float(os.environ.get("FAKE_START_JITTER_S", "0"))
+    if jitter:
+        # what eight processes creating CUDA contexts at once look like: staggered, seconds apart
+        import random
+        time.sleep(random.Random(os.getpid()).uniform(0, jitter))
     comm = ctx.symmetric_comm(1 << 20, nvls_bytes=4096)
     cli, prefix = comm._rdv
     scope, gen = comm._rdv_gen
