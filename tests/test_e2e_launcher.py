@@ -418,7 +418,7 @@ def test_killed_replica_reforms_the_gang_control_plane_version(world, tmp_path):
                         "pytorchReplicaSpecs": {"Master": spec(1), "Worker": spec(world - 1)}}}
         cli = PyTorchJobClient(cluster=cl)
         cli.create(job)
-        cli.wait_for_job("fake-restart", polling_interval=0.05, timeout_seconds=120)
+        cli.wait_for_job("fake-restart", polling_interval=0.05, timeout_seconds=300)
         logs = cli.get_logs("fake-restart", master=False)
         dump = "\n".join(f"--- {k}\n{v[-1500:]}" for k, v in logs.items())
         assert cli.is_job_succeeded("fake-restart"), dump
