@@ -72,6 +72,19 @@ def main():
     start_step = 0
     if args.checkpoint and os.path.exists(args.checkpoint):
         start_step = eng.load_checkpoint(args.checkpoint)
+    if comm is not None and getattr(comm, "_rdv", None) is not None:
+        # meet once more before the first collective: building the engine and loading the
+        # checkpoint take different times on different replicas, and the first all-reduce should
+        # not spend its spin limit on that. A peer that is gone by now means another restart round.
+        from tf_operator_b200.launcher.rendezvous import Superseded
+        cli, prefix = comm._rdv
+        scope, gen = getattr(comm, "_rdv_gen", ("", -1))
+        try:
+            cli.barrier(prefix + "/start", ctx.world_size, timeout=120, scope=scope, gen=gen)
+        except (Superseded, TimeoutError) as e:
+            print(f"rank {ctx.rank}: gang incomplete before the first step ({type(e).__name__}); "
+                  f"exiting 138 (retryable)", flush=True)
+            os._exit(138)
     torch.manual_seed(100 + ctx.rank)
     B, S = args.batch_size, args.image_size
     xs = [torch.randint(0, 256, (B, S, S, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
