@@ -51,6 +51,7 @@ def main():
     fault = os.environ.get("TFOP_FAULT_INJECT", "")
     f_rank, f_step, f_marker = (fault.split(":", 2) + ["", ""])[:3] if fault else ("", "", "")
     try:
+        cli.barrier(prefix + "/start", ctx.world_size, timeout=60, scope=scope, gen=gen)   # as train.py
         for step in range(start, steps):
             if fault and int(f_rank) == ctx.rank and step == int(f_step) and not os.path.exists(f_marker):
                 open(f_marker, "w").write(str(os.getpid()))
