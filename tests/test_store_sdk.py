@@ -274,3 +274,72 @@ def test_swagger_runtime_standins_roundtrip_models_over_rest():
         assert api.select_header_content_type([]) == "application/json"
         assert "SDK Package Version" in cfg.to_debug_report()
     Configuration.set_default(None)
+
+
+def test_store_indexes_agree_with_a_full_scan_under_random_mutation():
+    """ObjectStore.select (label and owner indexes) returns exactly what a walk over every object
+    would, after any mix of creates, label / owner edits, status updates and (cascading) deletes;
+    ``list(predicate=...)`` filters before it copies."""
+    import random
+    from tf_operator_b200.store.memory import ApiError, ObjectStore
+    rng = random.Random(7)
+    st = ObjectStore()
+    owners = [f"uid-{i}" for i in range(4)]
+    names = [f"p{i}" for i in range(40)]
+
+    def brute(labels, uid):
+        out = []
+        for o in st.list("pods", "default"):
+            md = o["metadata"]
+            lab = md.get("labels") or {}
+            if (labels and all(lab.get(k) == v for k, v in labels.items())) or \
+                    any(r.get("uid") == uid for r in md.get("ownerReferences") or []):
+                out.append(md["name"])
+        return sorted(out)
+
+    for step in range(600):
+        name = rng.choice(names)
+        op = rng.random()
+        try:
+            if op < 0.35:
+                md = {"name": name, "namespace": "default",
+                      "labels": {"job-name": f"j{rng.randrange(5)}", "replica-type": rng.choice(["ps", "worker"])}}
+                if rng.random() < 0.7:
+                    md["ownerReferences"] = [{"uid": rng.choice(owners), "controller": True, "kind": "TFJob",
+                                              "name": "x", "apiVersion": "kubeflow.org/v1"}]
+                st.create("pods", {"metadata": md, "spec": {}})
+            elif op < 0.55:
+                st.patch("pods", "default", name, {"metadata": {"labels": {"job-name": f"j{rng.randrange(5)}"}}})
+            elif op < 0.65:
+                st.patch("pods", "default", name, {"metadata": {"ownerReferences": None}})
+            elif op < 0.8:
+                p = st.get("pods", "default", name)
+                p.setdefault("status", {})["phase"] = "Running"
+                st.update_status("pods", p)
+            else:
+                st.delete("pods", "default", name)
+        except ApiError:
+            pass
+        if step % 10 == 0:
+            for j in range(5):
+                sel = {"job-name": f"j{j}"}
+                uid = rng.choice(owners)
+                assert [o["metadata"]["name"] for o in st.select("pods", "default", sel, uid)] == brute(sel, uid)
+                assert [o["metadata"]["name"] for o in st.select("pods", "default", sel)] == brute(sel, None)
+                two = {"job-name": f"j{j}", "replica-type": "ps"}
+                assert [o["metadata"]["name"] for o in st.select("pods", "default", two)] == brute(two, None)
+    # the predicate form of list copies only what it keeps, and sees the stored labels
+    hits = st.list("pods", "default", predicate=lambda o: (o["metadata"].get("labels") or {}).get("job-name") == "j1")
+    assert sorted(o["metadata"]["name"] for o in hits) == brute({"job-name": "j1"}, None)
+    # a cascading delete goes through the owner index
+    owner = st.create("tfjobs", {"apiVersion": "kubeflow.org/v1", "kind": "TFJob",
+                                 "metadata": {"name": "own", "namespace": "default"},
+                                 "spec": {"tfReplicaSpecs": {"Worker": {"replicas": 1, "template": {"spec": {
+                                     "containers": [{"name": "tensorflow", "image": "i"}]}}}}}})
+    for i in range(3):
+        st.create("pods", {"metadata": {"name": f"dep{i}", "namespace": "default", "ownerReferences": [
+            {"uid": owner["metadata"]["uid"], "controller": True, "kind": "TFJob", "name": "own",
+             "apiVersion": "kubeflow.org/v1"}]}, "spec": {}})
+    st.delete("tfjobs", "default", "own")
+    assert not [p for p in st.list("pods", "default") if p["metadata"]["name"].startswith("dep")]
+    assert st.select("pods", "default", {}, owner["metadata"]["uid"]) == []

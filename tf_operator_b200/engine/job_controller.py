@@ -104,6 +104,13 @@ class JobController:
     def get_services_for_job(self, job) -> List[Dict[str, Any]]:
         return self._claim("services", job)
 
+    def _list_candidates(self, resource: str, ns: str, selector, uid, predicate) -> List[Dict[str, Any]]:
+        select = getattr(self.store, "select", None)
+        if select is not None:      # indexed: cost proportional to the job's own objects
+            return select(resource, ns, selector, uid)
+        # a store without indexes (HTTP transport, fakes): list and filter
+        return [o for o in self.store.list(resource, ns) if predicate(o)]
+
     def _claim(self, resource: str, job) -> List[Dict[str, Any]]:
         if self.store is None:
             return []
@@ -111,7 +118,16 @@ class JobController:
         selector = self.gen_labels(c.name_of(job))
         uid = job.get("metadata", {}).get("uid")
         out = []
-        for obj in self.store.list(resource, ns):
+
+        def mine(obj) -> bool:
+            # candidates only: carries the job's labels (own or adoptable) or is owned by the job
+            # (labels may have drifted: release). Evaluated inside the store before the copy.
+            md = obj.get("metadata", {})
+            labels = md.get("labels") or {}
+            if all(labels.get(k) == v for k, v in selector.items()):
+                return True
+            return any(r.get("uid") == uid for r in md.get("ownerReferences") or [])
+        for obj in self._list_candidates(resource, ns, selector, uid, mine):
             labels = obj.get("metadata", {}).get("labels") or {}
             matches = all(labels.get(k) == v for k, v in selector.items())
             ref = c.get_controller_of(obj)
