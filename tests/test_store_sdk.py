@@ -343,3 +343,15 @@ def test_store_indexes_agree_with_a_full_scan_under_random_mutation():
     st.delete("tfjobs", "default", "own")
     assert not [p for p in st.list("pods", "default") if p["metadata"]["name"].startswith("dep")]
     assert st.select("pods", "default", {}, owner["metadata"]["uid"]) == []
+
+
+def test_store_keeps_a_bounded_number_of_events():
+    from tf_operator_b200.store.memory import ObjectStore
+    st = ObjectStore()
+    st.max_events = 50
+    pod = st.create("pods", {"metadata": {"name": "p", "namespace": "default"}, "spec": {}})
+    for i in range(180):
+        st.record_event(pod, "Normal", "Tick", f"event {i}")
+    evs = st.list("events", "default")
+    assert len(evs) == 50 and {e["message"] for e in evs} == {f"event {i}" for i in range(130, 180)}
+    assert len(st.audit) <= st.audit.maxlen

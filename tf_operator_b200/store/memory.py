@@ -15,6 +15,7 @@ our equivalent of both.
 """
 from __future__ import annotations
 
+import collections
 import copy
 import queue
 import threading
@@ -191,7 +192,12 @@ class ObjectStore:
         self._watches: List[Watch] = []
         self._listeners: List[Callable[[str, str, Dict[str, Any]], None]] = []
         # recording hooks, the equivalent of control.FakePodControl (controller_test.go:63-64)
-        self.audit: List[Tuple[str, str, str, str]] = []   # (verb, resource, ns, name)
+        # (verb, resource, ns, name) of the most recent writes; bounded, as is the number of Event
+        # objects kept (kube-apiserver drops events after an hour): a long-lived cluster must not
+        # grow with every reconcile it has ever done
+        self.audit: "collections.deque[Tuple[str, str, str, str]]" = collections.deque(maxlen=65536)
+        self.max_events = 20000
+        self._event_order: "collections.deque[Tuple[str, str, str]]" = collections.deque()
         self.admission_enabled = True
 
     # ---- helpers -----------------------------------------------------------
@@ -332,6 +338,12 @@ class ObjectStore:
                 obj.setdefault("status", {}).setdefault("phase", c.POD_PENDING)
             self._objs[key] = obj
             self._index(key, obj)
+            if resource == "events":
+                self._event_order.append(key)
+                while len(self._event_order) > self.max_events:
+                    old = self._event_order.popleft()
+                    if old in self._objs:
+                        self.delete("events", old[1], old[2])
             self.audit.append(("create", resource, ns, md["name"]))
             self._emit(resource, "ADDED", obj)
             return c.deepcopy(obj)
